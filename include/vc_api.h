@@ -1,0 +1,134 @@
+/* vc_api.h -- C-ABI of the B200 batched NMPC engine (libvc_b200.so).
+ *
+ * The reference (neverorfrog/vehicle-control) has no FFI of its own: the hot path sits behind
+ * Python classes that call CasADi/IPOPT.  Each entry point below replaces one of those call
+ * sites; the reference-side binding is a ctypes stub.
+ *
+ * Conventions
+ *   - every pointer argument named d_* is a DEVICE pointer to contiguous row-major memory owned by
+ *     the caller (fp64 unless stated int32); h_* are host pointers, copied during the call.
+ *   - all functions return 0 on success, <0 on error; vc_last_error() gives a thread-local message.
+ *   - work is enqueued on the handle's CUDA stream; no hidden device synchronisation except where
+ *     stated.  A handle is bound to one device and is not re-entrant.
+ *   - state order  SingleTrack: Ux Uy r delta s ey epsi t   (models/dynamic_car.py:246-247)
+ *                  PointMass  : V s ey epsi t              (models/dynamic_point_mass.py:155-156)
+ *     input order  SingleTrack: Fx w ; PointMass: Fx Fy     (dynamic_car.py:208-209, dynamic_point_mass.py:120-121)
+ */
+#ifndef VC_API_H
+#define VC_API_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* config/models/dynamic_car.yaml, flattened (consumed by models/dynamic_car.py:49-191) */
+typedef struct vc_model_params {
+    double dt;                 /* plant sampling time                      dynamic_car.yaml:1  */
+    double l, m, Izz, a, b, h, eps, Peng;
+    double Xdf, Xdr, Xbf, Xbr; /* drive / brake distribution                                   */
+    double Caf, Car;           /* cornering stiffness                                          */
+    double Cd, muf, mur, Av2, Frr;
+    double g_eff;              /* 9.88*cos(theta)*cos(phi)                 dynamic_car.py:61,98 */
+} vc_model_params;
+
+/* config/controllers/{singletrack,cascaded}.yaml (consumed by controllers/mpc/cascaded_mpc.py) */
+typedef struct vc_mpc_config {
+    int N;                     /* horizon      (SingleTrack stages)        cascaded_mpc.py:42   */
+    int M;                     /* horizon_pm   (PointMass stages)          cascaded_mpc.py:48   */
+    int obstacles;             /* 0/1                                      cascaded_mpc.py:173  */
+    int max_iter;              /* IPM iteration cap                                             */
+    double mpc_dt, ds_pm;
+    /* cost_weights */
+    double w_time, w_speed, w_ey, w_epsi, w_w, w_Fx, w_Fy, w_dev_st, w_dev_pm, w_boundary, w_slip,
+        w_obstacles, w_switch_F;
+    /* input / state constraints */
+    double w_min, w_max, Ux_min, max_speed, delta_min, delta_max, ey_min, ey_max;
+    double V_min, ey_min_pm, ey_max_pm;
+    /* interior-point options (IPOPT defaults used by the reference: cascaded_mpc.py:55-65) */
+    double tol;                /* 1e-8                                                          */
+    double acceptable_tol;     /* 1e-6                                                          */
+    int acceptable_iter;       /* 15                                                            */
+    int obj_scaling;           /* 1 = gradient-based objective scaling (max gradient 100)       */
+    double mu_init;            /* 0.1                                                           */
+    double bound_relax;        /* 1e-8                                                          */
+} vc_mpc_config;
+
+typedef struct vc_handle vc_handle;
+
+/* solver exit status written to d_status[b] by vc_nmpc_solve */
+enum { VC_SOLVED = 0, VC_ACCEPTABLE = 1, VC_MAX_ITER = 2, VC_EVAL_ERROR = 3, VC_LINESEARCH_FAIL = 4 };
+
+const char* vc_last_error(void);
+int vc_version(void);
+
+/* replaces: DynamicCar/DynamicPointMass/CascadedMPC construction (racing.py:43-63).  `stream`
+ * is a cudaStream_t (NULL = legacy default stream). */
+int vc_create(const vc_model_params* h_params, const vc_mpc_config* h_cfg, int device, void* stream,
+              vc_handle** out);
+int vc_destroy(vc_handle* h);
+int vc_set_config(vc_handle* h, const vc_mpc_config* h_cfg);
+
+/* replaces: Track._precompute_curvatures / Track.k (environment/track.py:156-167) and the x/y
+ * splines behind rel2glob (track.py:102-129,206-252).  Cubic not-a-knot B-spline COEFFICIENTS built
+ * on the host over uniformly spaced sites (curvature: k_x0 + i*k_step, i<n_k; x/y: integer waypoint
+ * index, i<n_xy, evaluated at s/length*n_xy); the knot vectors are arithmetic and not passed.
+ * Copied to the device here (synchronous).  h_x_coefs/h_y_coefs may be NULL if rel2glob is unused. */
+int vc_set_track(vc_handle* h, const double* h_k_coefs, int n_k, double k_x0, double k_step,
+                 const double* h_x_coefs, const double* h_y_coefs, int n_xy, double length);
+
+/* replaces: Track.k(s) for arrays (track.py:166). */
+int vc_track_curvature(vc_handle* h, int n, const double* d_s, double* d_kappa);
+
+/* replaces: Track.rel2glob (track.py:102-107) / CascadedMPC.get_state_prediction (cascaded_mpc.py:340-352).
+ * d_out[n,3] = (x, y, psi). */
+int vc_rel2glob(vc_handle* h, int n, const double* d_s, const double* d_ey, const double* d_epsi, double* d_out);
+
+/* replaces: CascadedMPC._init_horizon (cascaded_mpc.py:316-338): per-stage ds and curvature from
+ * the previous prediction.  d_Xprev[B,8,H] (only row Ux of the first N columns is read), d_x0[B,8]. */
+int vc_horizon_params(vc_handle* h, int B, const double* d_x0, const double* d_Xprev, double* d_ds,
+                      double* d_kappa);
+
+/* replaces: car.spatial_transition applied N times (dynamic_car.py:188-191) and CasADi's AD of it.
+ * d_X[B,N+1,8]; d_AB[B,N,8,10] = d x_{n+1} / d (x_n,u_n), may be NULL. */
+int vc_rollout_st(vc_handle* h, int B, int N, const double* d_x0, const double* d_U, const double* d_kappa,
+                  const double* d_ds, double* d_X, double* d_AB);
+
+/* replaces: point_mass.spatial_transition applied M times (dynamic_point_mass.py:100-103).
+ * d_X[B,M+1,5]; d_AB[B,M,5,7] may be NULL. */
+int vc_rollout_pm(vc_handle* h, int B, int M, const double* d_x0, const double* d_U, const double* d_kappa,
+                  const double* d_ds, double* d_X, double* d_AB);
+
+/* replaces: RacingCar.drive (racing_car.py:34-46): kappa = k(s); x <- RK4_t(x,u,kappa,dt) in place. */
+int vc_plant_step(vc_handle* h, int B, double* d_x, const double* d_u, double dt);
+
+/* replaces: the tyre helper Functions car.Fx_f/Fx_r/Fy_f/Fy_r/alpha_f/alpha_r (dynamic_car.py:79-142)
+ * for arrays.  d_out[B,6] = Fx_f Fx_r Fy_f Fy_r alpha_f alpha_r. */
+int vc_tyre_forces(vc_handle* h, int B, const double* d_x, const double* d_u, double* d_out);
+
+/* replaces: CascadedMPC.command -> opti.solve() (cascaded_mpc.py:306-314).  One NMPC instance per
+ * batch entry: primal-dual interior point with a per-instance Riccati KKT factorisation.
+ *   d_x0[B,8]; d_kappa[B,H]; d_ds[B,H]; d_obst[B,n_obs,3] = (s,ey,radius) or NULL;
+ *   d_X[B,8,H], d_U[B,2,H]: warm start in, solution out (layout of state_prediction / action_prediction);
+ *   d_obj[B]; d_status[B] int32; d_iters[B] int32; d_kkt[B] final scaled NLP error. */
+int vc_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_kappa, const double* d_ds,
+                  const double* d_obst, int n_obs, double* d_X, double* d_U, double* d_obj, int* d_status,
+                  int* d_iters, double* d_kkt);
+
+/* Objective / constraint residual of a given trajectory (no solve): diagnostics + parity tests.
+ * d_out[B,3] = objective, max equality violation, min inequality margin. */
+int vc_nmpc_eval(vc_handle* h, int B, const double* d_x0, const double* d_kappa, const double* d_ds,
+                 const double* d_obst, int n_obs, const double* d_X, const double* d_U, double* d_out);
+
+/* Host-buffer convenience wrapper of the same call (the e2e path): copies inputs H2D, solves,
+ * copies X,U,obj,status,iters back; synchronises the stream. */
+int vc_nmpc_solve_host(vc_handle* h, int B, const double* h_x0, const double* h_kappa, const double* h_ds,
+                       const double* h_obst, int n_obs, double* h_X, double* h_U, double* h_obj,
+                       int* h_status, int* h_iters, double* h_kkt);
+
+/* number of kernels this handle has launched so far (bench bookkeeping) */
+long long vc_launch_count(vc_handle* h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VC_API_H */

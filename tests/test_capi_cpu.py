@@ -1,0 +1,44 @@
+"""CPU: the C-ABI library builds, loads and exports every symbol include/vc_api.h declares."""
+import os
+import re
+
+import pytest
+
+from tests.conftest import ROOT
+
+
+def _declared():
+    src = open(os.path.join(ROOT, "include", "vc_api.h")).read()
+    return sorted(set(re.findall(r"\b(vc_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol():
+    from vehicle_control_b200 import _capi
+    lib = _capi.load()
+    names = _declared()
+    assert "vc_nmpc_solve" in names and "vc_rollout_st" in names
+    for n in names:
+        assert hasattr(lib, n), n
+    assert set(names) == set(_capi.EXPORTS), set(names) ^ set(_capi.EXPORTS)
+    assert lib.vc_version() >= 100
+
+
+def test_no_cpu_fallback_without_device():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from vehicle_control_b200.engine import Engine
+    from tests.conftest import load_yaml
+    with pytest.raises(RuntimeError):
+        Engine(load_yaml("models/dynamic_car.yaml"))
+
+
+def test_product_does_not_import_oracle():
+    bad = []
+    for d, _, fs in os.walk(os.path.join(ROOT, "vehicle_control_b200")):
+        for f in fs:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                txt = open(os.path.join(d, f)).read()
+                if re.search(r"^\s*(from|import)\s+oracle\b", txt, re.M):
+                    bad.append(f)
+    assert not bad, bad

@@ -1,0 +1,37 @@
+// Internal handle shared by the C-ABI translation units.
+#pragma once
+#include <cuda_runtime.h>
+#include <string>
+#include "../../include/vc_api.h"
+
+struct vc_handle {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    vc_model_params params{};
+    vc_mpc_config cfg{};
+    // track tables (device)
+    double* d_kc = nullptr;   // curvature spline coefficients [n_k]
+    int n_k = 0;
+    double k_x0 = 0.0, k_step = 0.05;
+    double* d_xc = nullptr;   // x(u) spline coefficients [n_xy]
+    double* d_yc = nullptr;
+    int n_xy = 0;
+    double length = 0.0;
+    int sm_count = 148;
+    int max_smem_optin = 0;
+    long long launches = 0;
+    // scratch for the host-buffer solve wrapper
+    void* d_scratch = nullptr;
+    size_t scratch_bytes = 0;
+};
+
+namespace vc {
+void set_error(const std::string& msg);
+int check_cuda(cudaError_t e, const char* what);
+// launchers implemented in vc_solver.cu
+int launch_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_kappa, const double* d_ds,
+                      const double* d_obst, int n_obs, double* d_X, double* d_U, double* d_obj, int* d_status,
+                      int* d_iters, double* d_kkt);
+int launch_nmpc_eval(vc_handle* h, int B, const double* d_x0, const double* d_kappa, const double* d_ds,
+                     const double* d_obst, int n_obs, const double* d_X, const double* d_U, double* d_out);
+}  // namespace vc

@@ -1,0 +1,384 @@
+// Batched dynamics kernels for sm_100a: SingleTrack RK4 rollout (+ exact Jacobians), PointMass Euler
+// rollout (+ Jacobians), track-spline lookups / horizon parameters, closed-loop plant step.
+// All arithmetic fp64; none of it is a dense contraction, so no tensor cores.
+#include "vc_handle.h"
+#include "vc_model.cuh"
+
+namespace vc {
+
+// ------------------------------------------------------------------------------------------------
+// K1a: SingleTrack spatial rollout, states only.  One thread per trajectory.
+// replaces car.spatial_transition chained N times (dynamic_car.py:188-191)
+__global__ void __launch_bounds__(128)
+k_rollout_st(Params p, int B, int N, const double* __restrict__ x0, const double* __restrict__ U,
+             const double* __restrict__ kappa, const double* __restrict__ ds, double* __restrict__ X) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    double x[8], xn[8], u[2];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) x[i] = x0[(size_t)b * 8 + i];
+    double* Xb = X + (size_t)b * (N + 1) * 8;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) Xb[i] = x[i];
+    for (int n = 0; n < N; ++n) {
+        const size_t bn = (size_t)b * N + n;
+        u[0] = U[bn * 2]; u[1] = U[bn * 2 + 1];
+        st_rk4<true>(p, x, u, kappa[bn], ds[bn], xn);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { x[i] = xn[i]; Xb[(n + 1) * 8 + i] = xn[i]; }
+    }
+}
+
+// K1b: SingleTrack spatial rollout with [A|B] = d x+ / d(x,u) (8x10 per step).
+// Eight lanes per trajectory; lane j carries the tangent along active input j
+// (Ux Uy r delta ey epsi | Fx w); columns s and t of A are unit vectors (f does not depend on s,t).
+// The 8x10 block is staged in shared memory so each trajectory-step is written as one 640-byte run.
+#define K1_TPB 128
+#define K1_GROUPS (K1_TPB / 8)
+__global__ void __launch_bounds__(K1_TPB)
+k_rollout_st_jac(Params p, int B, int N, const double* __restrict__ x0, const double* __restrict__ U,
+                 const double* __restrict__ kappa, const double* __restrict__ ds, double* __restrict__ X,
+                 double* __restrict__ AB) {
+    __shared__ double tile[K1_GROUPS][80];
+    const int g = threadIdx.x >> 3, j = threadIdx.x & 7;
+    const int b = blockIdx.x * K1_GROUPS + g;
+    const bool live = b < B;
+    const int bb = live ? b : B - 1;
+    // column of [A|B] owned by this lane
+    const int col = j < 4 ? j : (j < 6 ? j + 1 : j + 2);   // 0 1 2 3 5 6 8 9
+    double xv[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) xv[i] = x0[(size_t)bb * 8 + i];
+    double* Xb = X + (size_t)bb * (N + 1) * 8;
+    if (live) Xb[j] = xv[j];
+    for (int n = 0; n < N; ++n) {
+        const size_t bn = (size_t)bb * N + n;
+        Dual1 x[8], u[2], xn[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) x[i] = Dual1{xv[i], (col == i) ? 1.0 : 0.0};
+        u[0] = Dual1{U[bn * 2], col == 8 ? 1.0 : 0.0};
+        u[1] = Dual1{U[bn * 2 + 1], col == 9 ? 1.0 : 0.0};
+        st_rk4<true>(p, x, u, kappa[bn], ds[bn], xn);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            xv[i] = xn[i].v;
+            tile[g][i * 10 + col] = xn[i].d;
+        }
+        if (j == 0) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) { tile[g][i * 10 + 4] = (i == 4) ? 1.0 : 0.0; tile[g][i * 10 + 7] = (i == 7) ? 1.0 : 0.0; }
+        }
+        __syncwarp();
+        if (live) {
+            Xb[(n + 1) * 8 + j] = xv[j];
+            double* out = AB + bn * 80;
+#pragma unroll
+            for (int q = 0; q < 10; ++q) out[q * 8 + j] = tile[g][q * 8 + j];
+        }
+        __syncwarp();
+    }
+}
+
+// K2: PointMass spatial Euler rollout, optional [A|B] (5x7 per step).  One thread per trajectory.
+// replaces point_mass.spatial_transition (dynamic_point_mass.py:93-103)
+__global__ void __launch_bounds__(128)
+k_rollout_pm(Params p, int B, int M, const double* __restrict__ x0, const double* __restrict__ U,
+             const double* __restrict__ kappa, const double* __restrict__ ds, double* __restrict__ X,
+             double* __restrict__ AB) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    double x[5], xn[5], u[2];
+#pragma unroll
+    for (int i = 0; i < 5; ++i) x[i] = x0[(size_t)b * 5 + i];
+    double* Xb = X + (size_t)b * (M + 1) * 5;
+#pragma unroll
+    for (int i = 0; i < 5; ++i) Xb[i] = x[i];
+    for (int n = 0; n < M; ++n) {
+        const size_t bn = (size_t)b * M + n;
+        u[0] = U[bn * 2]; u[1] = U[bn * 2 + 1];
+        const double kp = kappa[bn], h = ds[bn];
+        pm_euler<true>(p, x, u, kp, h, xn);
+        if (AB) {
+            double* out = AB + bn * 35;
+            for (int c = 0; c < 7; ++c) {
+                Dual1 xd[5], ud[2], xo[5];
+#pragma unroll
+                for (int i = 0; i < 5; ++i) xd[i] = Dual1{x[i], c == i ? 1.0 : 0.0};
+                ud[0] = Dual1{u[0], c == 5 ? 1.0 : 0.0};
+                ud[1] = Dual1{u[1], c == 6 ? 1.0 : 0.0};
+                pm_euler<true>(p, xd, ud, kp, h, xo);
+#pragma unroll
+                for (int i = 0; i < 5; ++i) out[i * 7 + c] = xo[i].d;
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 5; ++i) { x[i] = xn[i]; Xb[(n + 1) * 5 + i] = xn[i]; }
+    }
+}
+
+// K3: horizon parameters (cascaded_mpc.py:316-338).  Persistent CTAs stage the curvature-spline
+// coefficient table in shared memory once, then sweep instances.
+__global__ void __launch_bounds__(256)
+k_horizon_params(int B, int N, int M, double mpc_dt, double ds_pm, const double* __restrict__ kc, UniformKnots kt,
+                 int use_smem, const double* __restrict__ x0, const double* __restrict__ Xprev,
+                 double* __restrict__ ds, double* __restrict__ kappa) {
+    extern __shared__ double s_c[];
+    const double* c = kc;
+    if (use_smem) {
+        for (int i = threadIdx.x; i < kt.n; i += blockDim.x) s_c[i] = kc[i];
+        __syncthreads();
+        c = s_c;
+    }
+    const int H = N + M;
+    for (int b = blockIdx.x * blockDim.x + threadIdx.x; b < B; b += gridDim.x * blockDim.x) {
+        const double* ux = Xprev + (size_t)b * 8 * H;   // row 0 (Ux) of state_prediction[8,H]
+        double* dsb = ds + (size_t)b * H;
+        double* kb = kappa + (size_t)b * H;
+        const double s0 = x0[(size_t)b * 8 + IS];
+        double cum = 0.0, d0 = 0.0, dlast = 0.0, slast = s0;
+        for (int n = 0; n < N; ++n) {
+            const double d = mpc_dt * ux[n];
+            if (n == 0) d0 = d;
+            cum += d;
+            const double s = cum - d0 + s0;
+            dsb[n] = d;
+            kb[n] = bspline3(c, kt, s, nullptr);
+            dlast = d; slast = s;
+        }
+        double cum_pm = 0.0;
+        for (int m = 0; m < M; ++m) {
+            cum_pm += ds_pm;
+            const double s = cum_pm - dlast + slast;
+            dsb[N + m] = ds_pm;
+            kb[N + m] = bspline3(c, kt, s, nullptr);
+        }
+    }
+}
+
+__global__ void k_curvature(int n, const double* __restrict__ kc, UniformKnots kt, const double* __restrict__ s,
+                            double* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = bspline3(kc, kt, s[i], nullptr);
+}
+
+// rel2glob (track.py:102-129): orientation from the spline tangent at fmod(s, L)
+__global__ void k_rel2glob(int n, const double* __restrict__ xc, const double* __restrict__ yc, UniformKnots kt,
+                           double length, const double* __restrict__ s, const double* __restrict__ ey,
+                           const double* __restrict__ epsi, double* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double scale = (double)kt.n / length;
+    const double sv = s[i];
+    const double sm = fmod(sv, length);
+    double dx, dy, tmp;
+    bspline3(xc, kt, sm * scale, &dx);
+    bspline3(yc, kt, sm * scale, &dy);
+    const double mag = sqrt(dx * dx + dy * dy);
+    const double th = atan2(dy / mag, dx / mag);
+    const double x = bspline3(xc, kt, sv * scale, &tmp);
+    const double y = bspline3(yc, kt, sv * scale, &tmp);
+    double sn, cs;
+    sincos(th, &sn, &cs);
+    double psi = th + epsi[i];
+    const double pi = 3.14159265358979323846;
+    if (psi < -pi) psi = 2 * pi + psi; else if (psi > pi) psi = psi - 2 * pi;   // common_utils.py:29-37
+    out[(size_t)i * 3 + 0] = x - sn * ey[i];
+    out[(size_t)i * 3 + 1] = y + cs * ey[i];
+    out[(size_t)i * 3 + 2] = psi;
+}
+
+// K5: closed-loop plant step (racing_car.py:34-46): kappa = k(s) (no fmod), temporal RK4.
+__global__ void __launch_bounds__(128)
+k_plant_step(Params p, int B, const double* __restrict__ kc, UniformKnots kt, double* __restrict__ x,
+             const double* __restrict__ u, double dt) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    double xv[8], xn[8], uv[2];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) xv[i] = x[(size_t)b * 8 + i];
+    uv[0] = u[(size_t)b * 2]; uv[1] = u[(size_t)b * 2 + 1];
+    const double kp = bspline3(kc, kt, xv[IS], nullptr);
+    st_rk4<false>(p, xv, uv, kp, dt, xn);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) x[(size_t)b * 8 + i] = xn[i];
+}
+
+__global__ void k_tyre_forces(Params p, int B, const double* __restrict__ x, const double* __restrict__ u,
+                              double* __restrict__ out) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    Tyres<double> ty;
+    tyres(p, x[(size_t)b * 8 + IUX], x[(size_t)b * 8 + IUY], x[(size_t)b * 8 + IR], x[(size_t)b * 8 + IDELTA],
+          u[(size_t)b * 2], ty);
+    double* o = out + (size_t)b * 6;
+    o[0] = ty.fxf; o[1] = ty.fxr; o[2] = ty.fyf; o[3] = ty.fyr; o[4] = ty.alpha_f; o[5] = ty.alpha_r;
+}
+
+}  // namespace vc
+
+// =================================================================================================
+// C-ABI (include/vc_api.h)
+// =================================================================================================
+namespace vc {
+static thread_local std::string g_err;
+void set_error(const std::string& msg) { g_err = msg; }
+int check_cuda(cudaError_t e, const char* what) {
+    if (e == cudaSuccess) return 0;
+    set_error(std::string(what) + ": " + cudaGetErrorString(e));
+    return -2;
+}
+static int bad(const char* msg) { set_error(msg); return -1; }
+static UniformKnots kknots(const vc_handle* h) { return UniformKnots{h->k_x0, h->k_step, h->n_k}; }
+static UniformKnots xyknots(const vc_handle* h) { return UniformKnots{0.0, 1.0, h->n_xy}; }
+}  // namespace vc
+
+using namespace vc;
+
+#define VC_REQUIRE(c, msg) do { if (!(c)) return bad(msg); } while (0)
+#define VC_LAUNCH_CHECK(h, what) do { (h)->launches++; int rc_ = check_cuda(cudaGetLastError(), what); if (rc_) return rc_; } while (0)
+
+extern "C" {
+
+const char* vc_last_error(void) { return g_err.c_str(); }
+int vc_version(void) { return 100; }
+
+int vc_create(const vc_model_params* hp, const vc_mpc_config* hc, int device, void* stream, vc_handle** out) {
+    VC_REQUIRE(hp && out, "vc_create: null argument");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev <= 0) {
+        set_error("vc_create: no CUDA device (this library has no CPU fallback)");
+        return -3;
+    }
+    VC_REQUIRE(device >= 0 && device < ndev, "vc_create: bad device index");
+    int rc = check_cuda(cudaSetDevice(device), "cudaSetDevice");
+    if (rc) return rc;
+    vc_handle* h = new vc_handle();
+    h->device = device;
+    h->stream = (cudaStream_t)stream;
+    h->params = *hp;
+    if (hc) h->cfg = *hc;
+    cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, device);
+    cudaDeviceGetAttribute(&h->max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
+    *out = h;
+    return 0;
+}
+
+int vc_destroy(vc_handle* h) {
+    if (!h) return 0;
+    cudaSetDevice(h->device);
+    cudaFree(h->d_kc); cudaFree(h->d_xc); cudaFree(h->d_yc); cudaFree(h->d_scratch);
+    delete h;
+    return 0;
+}
+
+int vc_set_config(vc_handle* h, const vc_mpc_config* hc) {
+    VC_REQUIRE(h && hc, "vc_set_config: null argument");
+    VC_REQUIRE(hc->N >= 1 && hc->M >= 0, "vc_set_config: need horizon N >= 1, M >= 0");
+    h->cfg = *hc;
+    return 0;
+}
+
+int vc_set_track(vc_handle* h, const double* kc, int n_k, double k_x0, double k_step, const double* xc,
+                 const double* yc, int n_xy, double length) {
+    VC_REQUIRE(h && kc && n_k >= 8 && k_step > 0, "vc_set_track: bad curvature table");
+    cudaSetDevice(h->device);
+    cudaFree(h->d_kc); cudaFree(h->d_xc); cudaFree(h->d_yc);
+    h->d_kc = h->d_xc = h->d_yc = nullptr;
+    int rc = check_cuda(cudaMalloc(&h->d_kc, sizeof(double) * n_k), "cudaMalloc(track)");
+    if (rc) return rc;
+    rc = check_cuda(cudaMemcpy(h->d_kc, kc, sizeof(double) * n_k, cudaMemcpyHostToDevice), "cudaMemcpy(track)");
+    if (rc) return rc;
+    h->n_k = n_k; h->k_x0 = k_x0; h->k_step = k_step; h->length = length; h->n_xy = 0;
+    if (xc && yc && n_xy >= 8) {
+        rc = check_cuda(cudaMalloc(&h->d_xc, sizeof(double) * n_xy), "cudaMalloc(track xy)");
+        if (rc) return rc;
+        rc = check_cuda(cudaMalloc(&h->d_yc, sizeof(double) * n_xy), "cudaMalloc(track xy)");
+        if (rc) return rc;
+        cudaMemcpy(h->d_xc, xc, sizeof(double) * n_xy, cudaMemcpyHostToDevice);
+        rc = check_cuda(cudaMemcpy(h->d_yc, yc, sizeof(double) * n_xy, cudaMemcpyHostToDevice), "cudaMemcpy(track xy)");
+        if (rc) return rc;
+        h->n_xy = n_xy;
+    }
+    return 0;
+}
+
+int vc_track_curvature(vc_handle* h, int n, const double* d_s, double* d_kappa) {
+    VC_REQUIRE(h && h->d_kc, "vc_track_curvature: track not set");
+    if (n <= 0) return 0;
+    k_curvature<<<(n + 255) / 256, 256, 0, h->stream>>>(n, h->d_kc, kknots(h), d_s, d_kappa);
+    VC_LAUNCH_CHECK(h, "k_curvature");
+    return 0;
+}
+
+int vc_rel2glob(vc_handle* h, int n, const double* d_s, const double* d_ey, const double* d_epsi, double* d_out) {
+    VC_REQUIRE(h && h->d_xc && h->d_yc, "vc_rel2glob: x/y spline tables not set");
+    if (n <= 0) return 0;
+    k_rel2glob<<<(n + 255) / 256, 256, 0, h->stream>>>(n, h->d_xc, h->d_yc, xyknots(h), h->length, d_s, d_ey,
+                                                        d_epsi, d_out);
+    VC_LAUNCH_CHECK(h, "k_rel2glob");
+    return 0;
+}
+
+int vc_horizon_params(vc_handle* h, int B, const double* d_x0, const double* d_Xprev, double* d_ds, double* d_kappa) {
+    VC_REQUIRE(h && h->d_kc, "vc_horizon_params: track not set");
+    VC_REQUIRE(h->cfg.N >= 1, "vc_horizon_params: config not set");
+    if (B <= 0) return 0;
+    const size_t smem = sizeof(double) * (size_t)h->n_k;
+    // stage the table in shared memory when it fits and there is enough work to amortise the fill
+    int use_smem = (smem <= (size_t)h->max_smem_optin && B >= 4 * h->sm_count) ? 1 : 0;
+    int grid = use_smem ? h->sm_count : (B + 255) / 256;
+    if (use_smem) {
+        int rc = check_cuda(cudaFuncSetAttribute(k_horizon_params, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
+                            "cudaFuncSetAttribute(k_horizon_params)");
+        if (rc) return rc;
+    }
+    k_horizon_params<<<grid, 256, use_smem ? smem : 0, h->stream>>>(B, h->cfg.N, h->cfg.M, h->cfg.mpc_dt, h->cfg.ds_pm,
+                                                                  h->d_kc, kknots(h), use_smem, d_x0, d_Xprev, d_ds,
+                                                                  d_kappa);
+    VC_LAUNCH_CHECK(h, "k_horizon_params");
+    return 0;
+}
+
+int vc_rollout_st(vc_handle* h, int B, int N, const double* d_x0, const double* d_U, const double* d_kappa,
+                  const double* d_ds, double* d_X, double* d_AB) {
+    VC_REQUIRE(h && N >= 0, "vc_rollout_st: bad argument");
+    if (B <= 0) return 0;
+    if (d_AB) {
+        k_rollout_st_jac<<<(B + K1_GROUPS - 1) / K1_GROUPS, K1_TPB, 0, h->stream>>>(h->params, B, N, d_x0, d_U, d_kappa,
+                                                                                 d_ds, d_X, d_AB);
+    } else {
+        k_rollout_st<<<(B + 127) / 128, 128, 0, h->stream>>>(h->params, B, N, d_x0, d_U, d_kappa, d_ds, d_X);
+    }
+    VC_LAUNCH_CHECK(h, "k_rollout_st");
+    return 0;
+}
+
+int vc_rollout_pm(vc_handle* h, int B, int M, const double* d_x0, const double* d_U, const double* d_kappa,
+                  const double* d_ds, double* d_X, double* d_AB) {
+    VC_REQUIRE(h && M >= 0, "vc_rollout_pm: bad argument");
+    if (B <= 0) return 0;
+    k_rollout_pm<<<(B + 127) / 128, 128, 0, h->stream>>>(h->params, B, M, d_x0, d_U, d_kappa, d_ds, d_X, d_AB);
+    VC_LAUNCH_CHECK(h, "k_rollout_pm");
+    return 0;
+}
+
+int vc_plant_step(vc_handle* h, int B, double* d_x, const double* d_u, double dt) {
+    VC_REQUIRE(h && h->d_kc, "vc_plant_step: track not set");
+    if (B <= 0) return 0;
+    k_plant_step<<<(B + 127) / 128, 128, 0, h->stream>>>(h->params, B, h->d_kc, kknots(h), d_x, d_u, dt);
+    VC_LAUNCH_CHECK(h, "k_plant_step");
+    return 0;
+}
+
+int vc_tyre_forces(vc_handle* h, int B, const double* d_x, const double* d_u, double* d_out) {
+    VC_REQUIRE(h, "vc_tyre_forces: null handle");
+    if (B <= 0) return 0;
+    k_tyre_forces<<<(B + 127) / 128, 128, 0, h->stream>>>(h->params, B, d_x, d_u, d_out);
+    VC_LAUNCH_CHECK(h, "k_tyre_forces");
+    return 0;
+}
+
+long long vc_launch_count(vc_handle* h) { return h ? h->launches : 0; }
+
+}  // extern "C"

@@ -1,0 +1,228 @@
+"""Batched device engine: thin torch-tensor front end of the C-ABI (include/vc_api.h).
+
+torch is used only as the owner of device memory / streams; every computation happens in the
+hand-written CUDA kernels of libvc_b200.so.  There is no CPU path: constructing an Engine without a
+CUDA device raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from typing import Optional
+
+import numpy as np
+import torch
+
+from . import _capi
+from ._capi import MpcConfig, ModelParams, check
+from .utils.common_utils import as_config
+
+STATUS_NAMES = {0: "solved", 1: "acceptable", 2: "max_iter", 3: "eval_error", 4: "linesearch_fail"}
+
+
+def model_params_from(cfg) -> ModelParams:
+    """config/models/dynamic_car.yaml -> vc_model_params (dynamic_car.py:61-102 naming)."""
+    cfg = as_config(cfg)
+    car, env = cfg.car, cfg.env
+    p = ModelParams()
+    p.dt = float(cfg.dt)
+    for k in ("l", "m", "Izz", "a", "b", "h", "eps", "Peng"):
+        setattr(p, k, float(car[k]))
+    p.Xdf, p.Xdr, p.Xbf, p.Xbr = float(car.Xd.f), float(car.Xd.r), float(car.Xb.f), float(car.Xb.r)
+    p.Caf, p.Car = float(car.C_alpha.f), float(car.C_alpha.r)
+    p.Cd, p.muf, p.mur = float(env.Cd), float(env.mu.f), float(env.mu.r)
+    p.Av2, p.Frr = float(env.Av2), float(env.Frr)
+    p.g_eff = 9.88 * math.cos(float(env.theta)) * math.cos(float(env.phi))
+    return p
+
+
+def mpc_config_from(cfg, **overrides) -> MpcConfig:
+    """config/controllers/*.yaml -> vc_mpc_config (keys read by cascaded_mpc.py)."""
+    cfg = as_config(cfg)
+    cw, ic, sc = cfg.cost_weights, cfg.input_constraints, cfg.state_constraints
+    pc = cfg.get("state_pm_constraints") or {}
+    c = MpcConfig()
+    c.N, c.M = int(cfg.horizon), int(cfg.horizon_pm)
+    c.obstacles = 1 if cfg.get("obstacles") else 0
+    c.max_iter = 300
+    c.mpc_dt, c.ds_pm = float(cfg.mpc_dt), float(cfg.ds_pm)
+    c.w_time, c.w_speed, c.w_ey, c.w_epsi = float(cw.time), float(cw.speed), float(cw.ey), float(cw.epsi)
+    c.w_w, c.w_Fx, c.w_Fy = float(cw.w), float(cw.Fx), float(cw.get("Fy", 0.0))
+    c.w_dev_st, c.w_dev_pm = float(cw.deviation_st), float(cw.get("deviation_pm", 0.0))
+    c.w_boundary, c.w_slip = float(cw.boundary), float(cw.slip)
+    c.w_obstacles, c.w_switch_F = float(cw.get("obstacles", 0.0)), float(cw.get("switch_F", 0.0))
+    c.w_min, c.w_max = float(ic.w_min), float(ic.w_max)
+    c.Ux_min, c.max_speed = float(sc.Ux_min), float(sc.max_speed)
+    c.delta_min, c.delta_max = float(sc.delta_min), float(sc.delta_max)
+    c.ey_min, c.ey_max = float(sc.ey_min), float(sc.ey_max)
+    c.V_min = float(pc.get("V_min", sc.Ux_min))
+    c.ey_min_pm, c.ey_max_pm = float(pc.get("ey_min", sc.ey_min)), float(pc.get("ey_max", sc.ey_max))
+    # IPOPT defaults the reference runs with (cascaded_mpc.py:55-65)
+    c.tol, c.acceptable_tol, c.acceptable_iter = 1e-8, 1e-6, 15
+    c.obj_scaling, c.mu_init, c.bound_relax = 1, 0.1, 1e-8
+    for k, v in overrides.items():
+        setattr(c, k, v)
+    return c
+
+
+class Engine:
+    def __init__(self, car_config, mpc_config=None, track=None, device: Optional[int] = None, stream=None):
+        self.lib = _capi.load()
+        if not torch.cuda.is_available():
+            raise RuntimeError("vehicle_control_b200.Engine needs a CUDA device: there is no CPU fallback")
+        self.device_index = torch.cuda.current_device() if device is None else int(device)
+        self.device = torch.device("cuda", self.device_index)
+        self.params = car_config if isinstance(car_config, ModelParams) else model_params_from(car_config)
+        self.cfg = None
+        h = C.c_void_p()
+        check(self.lib.vc_create(C.byref(self.params), None, self.device_index, stream, C.byref(h)), "vc_create")
+        self._h = h
+        self.track = None
+        if mpc_config is not None:
+            self.set_config(mpc_config)
+        if track is not None:
+            self.set_track(track)
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h:
+            try:
+                self.lib.vc_destroy(h)
+            except Exception:
+                pass
+            self._h = None
+
+    # ------------------------------------------------------------------ setup
+    def set_config(self, mpc_config, **overrides):
+        self.cfg = mpc_config if isinstance(mpc_config, MpcConfig) else mpc_config_from(mpc_config, **overrides)
+        check(self.lib.vc_set_config(self._h, C.byref(self.cfg)), "vc_set_config")
+
+    def set_track(self, track):
+        t = track.device_tables()
+        kc, xc, yc = t["k_coefs"], t["x_coefs"], t["y_coefs"]
+        check(self.lib.vc_set_track(self._h, kc.ctypes.data, len(kc), t["k_x0"], t["k_step"], xc.ctypes.data,
+                                    yc.ctypes.data, len(xc), t["length"]), "vc_set_track")
+        self.track = track
+
+    @property
+    def H(self):
+        return self.cfg.N + self.cfg.M
+
+    # ------------------------------------------------------------------ helpers
+    def tensor(self, a, dtype=torch.float64):
+        return torch.as_tensor(np.ascontiguousarray(a), dtype=dtype).to(self.device).contiguous()
+
+    def _p(self, t, shape=None, dtype=torch.float64):
+        if t is None:
+            return None
+        if not (isinstance(t, torch.Tensor) and t.is_cuda and t.dtype == dtype and t.is_contiguous()
+                and t.device.index == self.device_index):
+            raise TypeError(f"expected a contiguous {dtype} tensor on {self.device}")
+        if shape is not None and tuple(t.shape) != tuple(shape):
+            raise ValueError(f"expected shape {tuple(shape)}, got {tuple(t.shape)}")
+        return t.data_ptr()
+
+    def empty(self, *shape, dtype=torch.float64):
+        return torch.empty(*shape, dtype=dtype, device=self.device)
+
+    # ------------------------------------------------------------------ dynamics kernels
+    def rollout_st(self, x0, U, kappa, ds, jac=False):
+        B, N = U.shape[0], U.shape[1]
+        X = self.empty(B, N + 1, 8)
+        AB = self.empty(B, N, 8, 10) if jac else None
+        check(self.lib.vc_rollout_st(self._h, B, N, self._p(x0, (B, 8)), self._p(U, (B, N, 2)),
+                                     self._p(kappa, (B, N)), self._p(ds, (B, N)), self._p(X), self._p(AB)),
+              "vc_rollout_st")
+        return (X, AB) if jac else X
+
+    def rollout_st_into(self, x0, U, kappa, ds, X, AB=None):
+        B, N = U.shape[0], U.shape[1]
+        check(self.lib.vc_rollout_st(self._h, B, N, self._p(x0, (B, 8)), self._p(U, (B, N, 2)),
+                                     self._p(kappa, (B, N)), self._p(ds, (B, N)), self._p(X, (B, N + 1, 8)),
+                                     self._p(AB, (B, N, 8, 10)) if AB is not None else None), "vc_rollout_st")
+
+    def rollout_pm(self, x0, U, kappa, ds, jac=False):
+        B, M = U.shape[0], U.shape[1]
+        X = self.empty(B, M + 1, 5)
+        AB = self.empty(B, M, 5, 7) if jac else None
+        check(self.lib.vc_rollout_pm(self._h, B, M, self._p(x0, (B, 5)), self._p(U, (B, M, 2)),
+                                     self._p(kappa, (B, M)), self._p(ds, (B, M)), self._p(X), self._p(AB)),
+              "vc_rollout_pm")
+        return (X, AB) if jac else X
+
+    def plant_step(self, x, u, dt=None):
+        """In-place closed-loop plant step of every vehicle (racing_car.py:34-46)."""
+        B = x.shape[0]
+        check(self.lib.vc_plant_step(self._h, B, self._p(x, (B, 8)), self._p(u, (B, 2)),
+                                     float(self.params.dt if dt is None else dt)), "vc_plant_step")
+        return x
+
+    def tyre_forces(self, x, u):
+        B = x.shape[0]
+        out = self.empty(B, 6)
+        check(self.lib.vc_tyre_forces(self._h, B, self._p(x, (B, 8)), self._p(u, (B, 2)), self._p(out)),
+              "vc_tyre_forces")
+        return out
+
+    # ------------------------------------------------------------------ track kernels
+    def curvature(self, s):
+        out = torch.empty_like(s)
+        check(self.lib.vc_track_curvature(self._h, s.numel(), self._p(s), self._p(out)), "vc_track_curvature")
+        return out
+
+    def rel2glob(self, s, ey, epsi):
+        n = s.numel()
+        out = self.empty(*s.shape, 3)
+        check(self.lib.vc_rel2glob(self._h, n, self._p(s), self._p(ey), self._p(epsi), self._p(out)), "vc_rel2glob")
+        return out
+
+    def horizon_params(self, x0, Xprev, ds=None, kappa=None):
+        B, H = x0.shape[0], self.H
+        ds = self.empty(B, H) if ds is None else ds
+        kappa = self.empty(B, H) if kappa is None else kappa
+        check(self.lib.vc_horizon_params(self._h, B, self._p(x0, (B, 8)), self._p(Xprev, (B, 8, H)),
+                                         self._p(ds, (B, H)), self._p(kappa, (B, H))), "vc_horizon_params")
+        return ds, kappa
+
+    # ------------------------------------------------------------------ NMPC
+    def solve(self, x0, kappa, ds, X, U, obstacles=None, out=None):
+        """Batched NMPC solve (cascaded_mpc.py:306-314).  X[B,8,H], U[B,2,H] are warm start in / solution out.
+        Returns dict(obj, status, iters, kkt) of device tensors."""
+        B, H = x0.shape[0], self.H
+        if out is None:
+            out = {"obj": self.empty(B), "status": self.empty(B, dtype=torch.int32),
+                   "iters": self.empty(B, dtype=torch.int32), "kkt": self.empty(B)}
+        n_obs = 0 if obstacles is None else obstacles.shape[1]
+        check(self.lib.vc_nmpc_solve(self._h, B, self._p(x0, (B, 8)), self._p(kappa, (B, H)), self._p(ds, (B, H)),
+                                     self._p(obstacles, (B, n_obs, 3)) if n_obs else None, n_obs,
+                                     self._p(X, (B, 8, H)), self._p(U, (B, 2, H)), self._p(out["obj"]),
+                                     self._p(out["status"], dtype=torch.int32),
+                                     self._p(out["iters"], dtype=torch.int32), self._p(out["kkt"])), "vc_nmpc_solve")
+        return out
+
+    def evaluate(self, x0, kappa, ds, X, U, obstacles=None):
+        """[B,3] objective, max equality violation, min inequality margin of a given trajectory."""
+        B, H = x0.shape[0], self.H
+        out = self.empty(B, 3)
+        n_obs = 0 if obstacles is None else obstacles.shape[1]
+        check(self.lib.vc_nmpc_eval(self._h, B, self._p(x0, (B, 8)), self._p(kappa, (B, H)), self._p(ds, (B, H)),
+                                    self._p(obstacles, (B, n_obs, 3)) if n_obs else None, n_obs,
+                                    self._p(X, (B, 8, H)), self._p(U, (B, 2, H)), self._p(out)), "vc_nmpc_eval")
+        return out
+
+    def solve_host(self, x0, kappa, ds, X, U, obstacles=None):
+        """Host-buffer call (numpy in / out; X and U are updated in place).  Copies are inside the call."""
+        B, H = x0.shape[0], self.H
+        for a in (x0, kappa, ds, X, U):
+            assert a.dtype == np.float64 and a.flags.c_contiguous
+        obj, kkt = np.empty(B), np.empty(B)
+        status, iters = np.empty(B, np.int32), np.empty(B, np.int32)
+        n_obs = 0 if obstacles is None else obstacles.shape[1]
+        check(self.lib.vc_nmpc_solve_host(self._h, B, x0.ctypes.data, kappa.ctypes.data, ds.ctypes.data,
+                                          obstacles.ctypes.data if n_obs else None, n_obs, X.ctypes.data,
+                                          U.ctypes.data, obj.ctypes.data, status.ctypes.data, iters.ctypes.data,
+                                          kkt.ctypes.data), "vc_nmpc_solve_host")
+        return {"obj": obj, "status": status, "iters": iters, "kkt": kkt}
+
+    def launch_count(self) -> int:
+        return int(self.lib.vc_launch_count(self._h))
