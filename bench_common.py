@@ -92,3 +92,93 @@ def golden_states(track_name="ippodromo"):
         meta = json.load(f)
     rows = [z[k + "/state"][5:-1] for k, m in sorted(meta.items()) if m["track"] == track_name]
     return np.concatenate(rows, 0)
+
+
+# ------------------------------------------------------------------------------------------------
+# distributed plumbing (one process per GPU; instances shard with no data-path collective)
+def default_workload():
+    return "nmpc"
+
+
+def dist_setup(gpus):
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1 and not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29511")
+        import torch
+        dist.init_process_group("nccl" if torch.cuda.is_available() else "gloo", rank=rank, world_size=world)
+    return rank, world, local
+
+
+def dist_teardown():
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized():
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def barrier():
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized():
+        dist.barrier()
+
+
+def max_over_ranks(x: float) -> float:
+    import torch
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized():
+        t = torch.tensor([x], dtype=torch.float64, device="cuda" if torch.cuda.is_available() else "cpu")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+    return x
+
+
+def sum_over_ranks(x: float) -> float:
+    import torch
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized():
+        t = torch.tensor([x], dtype=torch.float64, device="cuda" if torch.cuda.is_available() else "cpu")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+    return x
+
+
+class L2Flusher:
+    """Writes a buffer larger than the 126 MB L2 between timed iterations."""
+
+    def __init__(self, device, mib=256):
+        import torch
+        self.buf = torch.empty(mib << 20, dtype=torch.uint8, device=device)
+        self.k = 0
+
+    def __call__(self):
+        self.k = (self.k + 1) & 0x7F
+        self.buf.fill_(self.k)
+
+
+def time_steps(step_fn, steps, warmup, flush=None, per_step_events=True):
+    """W untimed warm-up steps, then exactly K timed steps between barrier+synchronize on both sides.
+    Returns (total_ms over the K steps excluding flushes, max over ranks; list of per-step ms on this rank)."""
+    import torch
+    for _ in range(warmup):
+        if flush:
+            flush()
+        step_fn()
+    torch.cuda.synchronize()
+    barrier()
+    torch.cuda.synchronize()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    for i in range(steps):
+        if flush:
+            flush()
+        ev[i][0].record()
+        step_fn()
+        ev[i][1].record()
+    torch.cuda.synchronize()
+    barrier()
+    torch.cuda.synchronize()
+    per = [a.elapsed_time(b) for a, b in ev]
+    return max_over_ranks(sum(per)), per
