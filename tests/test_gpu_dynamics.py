@@ -103,7 +103,12 @@ def test_curvature_rel2glob_and_horizon(eng, oracle_tracks, golden):
     sg = np.abs(s)
     out = eng.rel2glob(eng.tensor(sg), eng.tensor(ey), eng.tensor(ep)).cpu().numpy()
     x, y, psi = T.rel2glob(sg, ey, ep)
-    assert np.abs(out[:, 0] - x).max() < 1e-9 and np.abs(out[:, 1] - y).max() < 1e-9
+    # inside the table: 1e-9; beyond the finish line both sides extrapolate the end cubic (x/y are evaluated
+    # without fmod, track.py:102-107), which amplifies rounding by (distance in knots)^3 -> looser bar there
+    inside = sg <= T.length
+    for col, ref in ((0, x), (1, y)):
+        assert np.abs(out[inside, col] - ref[inside]).max() < 1e-9
+        assert (np.abs(out[~inside, col] - ref[~inside]) / np.maximum(1.0, np.abs(ref[~inside]))).max() < 1e-6
     d = np.abs(out[:, 2] - psi); d = np.minimum(d, 2 * np.pi - d)
     assert d.max() < 1e-9
     # horizon parameters (cascaded_mpc.py:316-338), both code paths (global table / smem-staged table)
