@@ -43,6 +43,8 @@ class IpmOptions:
     delta: float = 1.0
     s_theta: float = 1.1
     s_phi: float = 2.3
+    max_backtrack: int = 12
+    max_restorations: int = 2
     verbose: bool = False
     obj_scale: float = 0.0     # >0: use this objective scaling instead of computing it at w0
 
@@ -83,6 +85,21 @@ def _inertia(d):
 
 
 def solve(nlp, w0, opt: IpmOptions = IpmOptions()) -> IpmResult:
+    """IPM with the restoration substitute: if the filter line search finds no acceptable step, the
+    iterate is re-initialised by NLP.repair (dynamic rollout) and the barrier loop restarts, keeping the
+    objective scaling of the ORIGINAL initial point (that scaling decides where IPOPT's answer sits)."""
+    res = _solve_once(nlp, w0, opt)
+    restarts = 0
+    while res.status == "linesearch_fail" and restarts < opt.max_restorations and hasattr(nlp, "repair"):
+        restarts += 1
+        o2 = IpmOptions(**{**opt.__dict__, "obj_scale": res.obj_scale})
+        r2 = _solve_once(nlp, nlp.repair(res.w), o2)
+        r2.iters += res.iters + 1
+        res = r2
+    return res
+
+
+def _solve_once(nlp, w0, opt: IpmOptions) -> IpmResult:
     w = np.array(w0, dtype=float)
     n = w.size
     # objective scaling from the gradient at the initial guess
@@ -143,71 +160,80 @@ def solve(nlp, w0, opt: IpmOptions = IpmOptions()) -> IpmResult:
         rc = cv - s
         Hc = W + Jc.T @ (sig[:, None] * Jc)
         rhs_x = -(sf * gf + Jg.T @ lam - Jc.T @ (mu / s - sig * rc))
-        dw = dlam = None
-        trial = 0.0
         first_ever = delta_last == 0.0
-        while True:
-            K = np.zeros((n + me, n + me))
-            K[:n, :n] = Hc + trial * np.eye(n)
-            K[:n, n:] = Jg.T
-            K[n:, :n] = Jg
-            try:
-                L, D, perm = sla.ldl(K, lower=True)
-                pos, neg, zero = _inertia(D)
-            except Exception:
-                pos = neg = zero = -1
-            if pos == n and neg == me:
-                sol = np.linalg.solve(K, np.concatenate([rhs_x, -gv]))
-                dw, dlam = sol[:n], sol[n:]
-                if trial > 0:
-                    delta_last = trial
-                break
-            if trial == 0.0:
-                trial = 1e-4 if delta_last == 0.0 else max(1e-20, delta_last / 3.0)
-            else:
-                trial *= 100.0 if first_ever else 8.0
-            if trial > 1e40:
-                return IpmResult(w, fv, "linesearch_fail", it, err0, mu, lam, z, sf)
-        dsl = Jc @ dw + rc
-        dz = mu / s - z - sig * dsl
-        # fraction to the boundary
-        neg_s = dsl < 0
-        a_p = min(1.0, float((-tau * s[neg_s] / dsl[neg_s]).min())) if neg_s.any() else 1.0
-        neg_z = dz < 0
-        a_d = min(1.0, float((-tau * z[neg_z] / dz[neg_z]).min())) if neg_z.any() else 1.0
-        # filter line search on (theta, phi)
         theta = np.abs(gv).sum() + np.abs(rc).sum()
         phi = sf * fv - mu * np.log(s).sum()
-        dphi = sf * gf @ dw - mu * (dsl / s).sum()
         if theta0 is None:
             theta0 = theta
         theta_min = 1e-4 * max(1.0, theta0)
         theta_max = 1e4 * max(1.0, theta0)
-        alpha = a_p
+        trial = 0.0
         accepted = False
-        for _ in range(40):
-            wt, st = w + alpha * dw, s + alpha * dsl
-            ft, gt, ct = nlp.values(wt)
-            ok = np.isfinite(ft) and np.isfinite(gt).all() and np.isfinite(ct).all()
-            if ok:
-                th_t = np.abs(gt).sum() + np.abs(ct - st).sum()
-                ph_t = sf * ft - mu * np.log(st).sum()
-                in_filter = any(th_t >= ft_ and ph_t >= fp_ for ft_, fp_ in filt) or th_t > theta_max
-                if not in_filter:
-                    switching = (theta <= theta_min and dphi < 0 and
-                                 alpha * (-dphi) ** opt.s_phi > opt.delta * theta ** opt.s_theta)
-                    if switching:
-                        if ph_t <= phi + opt.eta_phi * alpha * dphi:
-                            accepted = True
-                    elif th_t <= (1 - opt.gamma_theta) * theta or ph_t <= phi - opt.gamma_phi * theta:
-                        accepted = True
-                        filt.append(((1 - opt.gamma_theta) * theta, phi - opt.gamma_phi * theta))
-                    # tiny steps at the noise floor: accept if both measures are unchanged to rounding
-                    if not accepted and abs(ph_t - phi) <= 1e-13 * max(1.0, abs(phi)) and th_t <= theta + 1e-13:
-                        accepted = True
-                if accepted:
+        while not accepted:
+            # ---- inertia-correcting factorisation (delta_w ladder)
+            while True:
+                K = np.zeros((n + me, n + me))
+                K[:n, :n] = Hc + trial * np.eye(n)
+                K[:n, n:] = Jg.T
+                K[n:, :n] = Jg
+                try:
+                    L, D, perm = sla.ldl(K, lower=True)
+                    pos, neg, zero = _inertia(D)
+                except Exception:
+                    pos = neg = zero = -1
+                if pos == n and neg == me:
+                    sol = np.linalg.solve(K, np.concatenate([rhs_x, -gv]))
+                    dw, dlam = sol[:n], sol[n:]
                     break
-            alpha *= 0.5
+                if trial == 0.0:
+                    trial = 1e-4 if delta_last == 0.0 else max(1e-20, delta_last / 3.0)
+                else:
+                    trial *= 100.0 if first_ever else 8.0
+                if trial > 1e40:
+                    return IpmResult(w, fv, "linesearch_fail", it, err0, mu, lam, z, sf)
+            dsl = Jc @ dw + rc
+            dz = mu / s - z - sig * dsl
+            # fraction to the boundary
+            neg_s = dsl < 0
+            a_p = min(1.0, float((-tau * s[neg_s] / dsl[neg_s]).min())) if neg_s.any() else 1.0
+            neg_z = dz < 0
+            a_d = min(1.0, float((-tau * z[neg_z] / dz[neg_z]).min())) if neg_z.any() else 1.0
+            # ---- filter line search on (theta, phi)
+            dphi = sf * gf @ dw - mu * (dsl / s).sum()
+            alpha = a_p
+            for _ in range(opt.max_backtrack):
+                wt, st = w + alpha * dw, s + alpha * dsl
+                ft, gt, ct = nlp.values(wt)
+                ok = np.isfinite(ft) and np.isfinite(gt).all() and np.isfinite(ct).all()
+                if ok:
+                    th_t = np.abs(gt).sum() + np.abs(ct - st).sum()
+                    ph_t = sf * ft - mu * np.log(st).sum()
+                    in_filter = any(th_t >= ft_ and ph_t >= fp_ for ft_, fp_ in filt) or th_t > theta_max
+                    if not in_filter:
+                        switching = (theta <= theta_min and dphi < 0 and
+                                     alpha * (-dphi) ** opt.s_phi > opt.delta * theta ** opt.s_theta)
+                        if switching:
+                            if ph_t <= phi + opt.eta_phi * alpha * dphi:
+                                accepted = True
+                        elif th_t <= (1 - opt.gamma_theta) * theta or ph_t <= phi - opt.gamma_phi * theta:
+                            accepted = True
+                            filt.append(((1 - opt.gamma_theta) * theta, phi - opt.gamma_phi * theta))
+                        # tiny steps at the noise floor: accept if both measures are unchanged to rounding
+                        if not accepted and abs(ph_t - phi) <= 1e-13 * max(1.0, abs(phi)) and th_t <= theta + 1e-13:
+                            accepted = True
+                    if accepted:
+                        break
+                alpha *= 0.5
+            if accepted:
+                if trial > 0:
+                    delta_last = trial
+                break
+            # No acceptable step along this direction.  IPOPT would enter its restoration phase here; this
+            # restatement instead damps the step (Levenberg-Marquardt style: a larger delta_w turns the
+            # direction towards the least-norm feasibility step, which the filter accepts) and retries.
+            trial = max(trial, 1e-4) * 100.0
+            if trial > 1e12:
+                break
         if not accepted:
             status = "linesearch_fail"
             break

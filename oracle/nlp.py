@@ -225,6 +225,32 @@ class NLP:
             out.append(torch.stack([V - lo(c.V_min), p.Peng / V - Fxp + rl], 1).reshape(-1))
         return torch.cat(out)
 
+
+    # ------------------------------------------------------------ restoration substitute
+    def repair(self, w_np, neutral=True):
+        """Dynamically feasible re-initialisation used where IPOPT would enter its restoration phase:
+        controls clipped to their bounds, states re-generated by rolling the models out from x0."""
+        c, p, N, M = self.cfg, self.p, self.N, self.M
+        X, U = self.unpack(w_np)
+        X, U = X.copy(), U.copy()
+        kap, ds = self.kappa.numpy(), self.ds.numpy()
+        if neutral:   # guess-independent: coast straight ahead, PointMass holds the centre line
+            U[0, :] = 0.0
+            U[1, :] = 0.0
+        else:
+            U[1, :N] = np.clip(U[1, :N], c.w_min, c.w_max)
+        X[:, 0] = self.x0.numpy()
+        for n in range(N - 1):
+            X[:, n + 1] = om.st_step_spatial(np, p, X[:, n][None], U[:, n][None], kap[n], ds[n])[0]
+        if M > 0:
+            xl = X[:, N - 1]
+            X[:5, N] = [np.hypot(xl[0], xl[1]), xl[4], xl[5], np.arctan(xl[1] / xl[0]) + xl[6], xl[7]]
+            for m in range(N, N + M - 1):
+                if neutral:
+                    U[1, m] = p.m * X[0, m] ** 2 * kap[m]
+                X[:5, m + 1] = om.pm_step_spatial(np, p, X[:5, m][None], U[:, m][None], kap[m], ds[m])[0]
+        return self.pack(X, U)
+
     # ------------------------------------------------------------ derivatives (exact, autodiff)
     def eval_all(self, w_np, lam_g, lam_c, obj_scale=1.0):
         """Returns f, grad f, g, Jg, c, Jc, W = hess(obj_scale*f + lam_g.g - lam_c.c)."""

@@ -23,6 +23,12 @@ struct vc_handle {
     // scratch for the host-buffer solve wrapper
     void* d_scratch = nullptr;
     size_t scratch_bytes = 0;
+    // NMPC solver workspace
+    void* d_ws = nullptr;
+    size_t ws_bytes = 0;
+    int* d_active = nullptr;
+    int* h_active = nullptr;
+    int last_passes = 0;
 };
 
 namespace vc {

@@ -268,6 +268,8 @@ int vc_destroy(vc_handle* h) {
     if (!h) return 0;
     cudaSetDevice(h->device);
     cudaFree(h->d_kc); cudaFree(h->d_xc); cudaFree(h->d_yc); cudaFree(h->d_scratch);
+    cudaFree(h->d_ws); cudaFree(h->d_active);
+    if (h->h_active) cudaFreeHost(h->h_active);
     delete h;
     return 0;
 }

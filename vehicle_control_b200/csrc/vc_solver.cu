@@ -1,8 +1,1016 @@
-// placeholder -- replaced by the batched interior-point NMPC solver
+// Batched NMPC solve for sm_100a: primal-dual interior point (IPOPT's published algorithm: monotone barrier,
+// filter line search, inertia correction) with a per-instance Riccati factorisation of the KKT system.
+//
+// Replaces CascadedMPC.command -> opti.solve() (vehicle_control/controllers/mpc/cascaded_mpc.py:306-314), i.e.
+// CasADi's AD (exact Lagrangian Hessian, "expand": True, :65) + IPOPT (:54-66) + the HSL MA27 LDL^T.
+//
+// Kernels per interior-point iteration (host-driven loop, all instances in lock step, finished ones idle):
+//   k_eval_st / k_eval_pm  one thread per (instance, stage, derivative pair): hyper-dual evaluation of the
+//                          stage Lagrangian -> exact Hessian block, dynamics/constraint Jacobians, gradients.
+//   k_step                 one warp per instance: error / barrier update (warp-shuffle reductions), block
+//                          tridiagonal KKT solve by Riccati recursion staged in shared memory (with the
+//                          delta_w inertia ladder), fraction-to-boundary, filter line search with lanes over
+//                          stages, primal-dual update; restoration substitute = dynamic re-rollout.
+// All fp64; per-stage matrices are <= 11x11, so there is nothing for tensor cores here.
+#include <cstdio>
+#include <cstring>
+#include <cstdlib>
+#include <vector>
 #include "vc_handle.h"
+#include "vc_nlp.cuh"
+
 namespace vc {
-int launch_nmpc_solve(vc_handle*, int, const double*, const double*, const double*, const double*, int, double*,
-                      double*, double*, int*, int*, double*) { set_error("nmpc solver not built"); return -9; }
-int launch_nmpc_eval(vc_handle*, int, const double*, const double*, const double*, const double*, int,
-                     const double*, const double*, double*) { set_error("nmpc solver not built"); return -9; }
+
+// ------------------------------------------------------------------------------------------------
+// per-instance workspace (global memory, one contiguous slab per instance so that a warp streams it)
+enum WsArray {
+    W_Y = 0,     // [H][10] stage variables (x,u); PointMass stages use 7
+    W_LAM,       // [H][8]  multiplier of the equality that defines x_k (k=0: initial state)
+    W_S,         // [H][10] slacks of the stage inequalities
+    W_Z,         // [H][10] their multipliers
+    W_HC,        // [H][36] condensed Hessian block, packed lower triangle over the ACTIVE stage variables
+    W_AB,        // [H][80] d(next state)/d(active vars): [i][a] stride 8; switch stage: row 5 = grad T
+    W_JC,        // [H][80] inequality Jacobian [j][a] stride 8
+    W_RD,        // [H][10] dual infeasibility  (eval: active entries; step: s, t, slew, obstacle parts)
+    W_GF,        // [H][10] scaled objective gradient
+    W_V1,        // [H][10] Jc^T (1/s)
+    W_V2,        // [H][10] Jc^T (z c / s)
+    W_GRES,      // [H][8]  equality residual of the row block that defines x_k
+    W_CRES,      // [H][10] inequality values c(y_k)
+    W_FST,       // [H][1]  stage cost (unscaled; AD part only)
+    W_OBS,       // [H][6]  obstacle term: value, d/ds, d/dey, ss, s-ey, ey-ey
+    W_DY,        // [H][10] primal direction
+    W_DLAM,      // [H][8]
+    W_DSL,       // [H][10]
+    W_DZ,        // [H][10]
+    W_PM,        // [H][100] Riccati cost-to-go Hessians
+    W_PV,        // [H][10]
+    W_KM,        // [H][24]  feedback gains K[2][10], kff[2]
+    W_COUNT
+};
+__host__ __device__ constexpr int ws_width(int a) {
+    return a == W_Y ? 10 : a == W_LAM ? 8 : a == W_S ? 10 : a == W_Z ? 10 : a == W_HC ? 36 : a == W_AB ? 80
+         : a == W_JC ? 80 : a == W_RD ? 10 : a == W_GF ? 10 : a == W_V1 ? 10 : a == W_V2 ? 10 : a == W_GRES ? 8
+         : a == W_CRES ? 10 : a == W_FST ? 1 : a == W_OBS ? 6 : a == W_DY ? 10 : a == W_DLAM ? 8 : a == W_DSL ? 10
+         : a == W_DZ ? 10 : a == W_PM ? 100 : a == W_PV ? 10 : a == W_KM ? 24 : 0;
 }
+__host__ __device__ constexpr int ws_offset(int a) {   // offset in doubles PER STAGE before array a
+    int o = 0;
+    for (int i = 0; i < a; ++i) o += ws_width(i);
+    return o;
+}
+constexpr int WS_PER_STAGE = ws_offset(W_COUNT);
+constexpr int NSCAL = 64;
+// scalar block of an instance
+enum Scal { S_MU = 0, S_SF, S_DELTA_LAST, S_THETA0, S_NFILT, S_ACC, S_MODE, S_RESTARTS, S_OBJ, S_ERR, S_ITERS,
+            S_STATUS, S_FILT = 16 /* theta[16] */, S_FILP = 32 /* phi[16] */ };
+constexpr int FILT_MAX = 16;
+enum Mode { MODE_INIT = 0, MODE_STEP = 1, MODE_DONE = 2, MODE_REINIT = 3 };
+
+struct Ws {
+    double* base;
+    int H;
+    size_t stride;   // doubles per instance
+    __host__ __device__ double* arr(int b, int a) const { return base + (size_t)b * stride + (size_t)ws_offset(a) * H; }
+    __host__ __device__ double* at(int b, int a, int k) const { return arr(b, a) + (size_t)k * ws_width(a); }
+    __host__ __device__ double* scal(int b) const { return base + (size_t)b * stride + (size_t)WS_PER_STAGE * H; }
+};
+
+struct Prob {   // device-side view of one vc_nmpc_solve call
+    Params p;
+    Cfg c;
+    int B, N, M, H, n_obs;
+    const double *x0, *kappa, *ds, *obst;
+    double *X, *U, *obj, *kkt;
+    int *status, *iters;
+};
+
+// active (differentiated) stage variables
+__device__ __constant__ int c_act_st[8] = {IUX, IUY, IR, IDELTA, IEY, IEPSI, YFX, YW};
+__device__ __constant__ int c_act_pm[5] = {QV, QEY, QEPSI, QFX, QFY};
+
+__device__ __forceinline__ void pair_from_index(int q, int& a, int& b) {   // q -> (a >= b), packed lower triangle
+    a = 0;
+    while ((a + 1) * (a + 2) / 2 <= q) ++a;
+    b = q - a * (a + 1) / 2;
+}
+
+// ------------------------------------------------------------------------------------------------
+// k_prepare: user layout X[B,8,H], U[B,2,H] (state_prediction / action_prediction) -> stage-major workspace
+__global__ void k_prepare(Prob pr, Ws ws) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= pr.B * pr.H) return;
+    const int b = t / pr.H, k = t % pr.H, H = pr.H;
+    const double* Xb = pr.X + (size_t)b * 8 * H;
+    const double* Ub = pr.U + (size_t)b * 2 * H;
+    double* y = ws.at(b, W_Y, k);
+    if (k < pr.N) {
+        for (int i = 0; i < 8; ++i) y[i] = Xb[i * H + k];
+        y[8] = Ub[k]; y[9] = Ub[H + k];
+    } else {
+        for (int i = 0; i < 5; ++i) y[i] = Xb[i * H + k];
+        y[5] = Ub[k]; y[6] = Ub[H + k]; y[7] = y[8] = y[9] = 0.0;
+    }
+    double *lam = ws.at(b, W_LAM, k), *s = ws.at(b, W_S, k), *z = ws.at(b, W_Z, k);
+    for (int i = 0; i < 8; ++i) lam[i] = 0.0;
+    for (int i = 0; i < 10; ++i) { s[i] = 1.0; z[i] = 0.0; }
+    if (k == 0) {
+        double* sc = ws.scal(b);
+        for (int i = 0; i < NSCAL; ++i) sc[i] = 0.0;
+        sc[S_MU] = pr.c.mu_init; sc[S_SF] = 1.0; sc[S_THETA0] = -1.0; sc[S_MODE] = MODE_INIT; sc[S_STATUS] = -1.0;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// k_eval_st: one thread per (instance, SingleTrack stage, pair (a,b) of active variables).  The stage's
+// Lagrangian terms are evaluated once in hyper-dual arithmetic seeded along (a,b): values, d/da, d/db, d2/dadb.
+__global__ void __launch_bounds__(128) k_eval_st(Prob pr, Ws ws) {
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const int N = pr.N;
+    if (t >= (long long)pr.B * N * 36) return;
+    const int q = (int)(t % 36), k = (int)((t / 36) % N), b = (int)(t / (36LL * N));
+    const double* sc = ws.scal(b);
+    if (sc[S_MODE] == MODE_DONE) return;
+    int ia, ib;
+    pair_from_index(q, ia, ib);
+    const int va = c_act_st[ia], vb = c_act_st[ib];
+    const bool diag = ia == ib;
+    const double* yv = ws.at(b, W_Y, k);
+    HDual y[10];
+#pragma unroll
+    for (int i = 0; i < 10; ++i) y[i] = HDual{yv[i], i == va ? 1.0 : 0.0, i == vb ? 1.0 : 0.0, 0.0};
+    const double sf = sc[S_SF];
+    const double kap = pr.kappa[(size_t)b * pr.H + k], ds = pr.ds[(size_t)b * pr.H + k];
+    const bool last_st = k == N - 1;
+    HDual cost, ineq[NI_ST];
+    st_cost_ineq(pr.p, pr.c, y, ds, last_st && pr.M == 0, cost, ineq);
+    const double *z = ws.at(b, W_Z, k), *s = ws.at(b, W_S, k);
+    double hab = sf * cost.ab, ga = sf * cost.a, rda, v1 = 0.0, v2 = 0.0;
+    rda = ga;
+    double* jc = ws.at(b, W_JC, k);
+#pragma unroll
+    for (int j = 0; j < NI_ST; ++j) {
+        const double zj = z[j], is = 1.0 / s[j];
+        hab += -zj * ineq[j].ab + zj * is * ineq[j].a * ineq[j].b;
+        rda -= zj * ineq[j].a;
+        v1 += ineq[j].a * is;
+        v2 += ineq[j].a * zj * ineq[j].v * is;
+        if (diag) jc[j * 8 + ia] = ineq[j].a;
+    }
+    double* ab = ws.at(b, W_AB, k);
+    if (!last_st) {
+        HDual xn[8];
+        st_rk4<true>(pr.p, y, y + 8, kap, ds, xn);
+        const double* lam = ws.at(b, W_LAM, k + 1);
+        const double* yn = ws.at(b, W_Y, k + 1);
+        double* gres = ws.at(b, W_GRES, k + 1);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            hab -= lam[i] * xn[i].ab;
+            rda -= lam[i] * xn[i].a;
+            if (diag) ab[i * 8 + ia] = xn[i].a;
+            if (q == 0) gres[i] = yn[i] - xn[i].v;
+        }
+    } else if (pr.M > 0) {
+        HDual xp[5], T;
+        st_switch(pr.p, y, xp, T);
+        const double* lam = ws.at(b, W_LAM, k + 1);
+        const double* yn = ws.at(b, W_Y, k + 1);
+        double* gres = ws.at(b, W_GRES, k + 1);
+#pragma unroll
+        for (int i = 0; i < 5; ++i) {
+            hab -= lam[i] * xp[i].ab;
+            rda -= lam[i] * xp[i].a;
+            if (diag) ab[i * 8 + ia] = xp[i].a;
+            if (q == 0) gres[i] = yn[i] - xp[i].v;
+        }
+        // switching cost sf*W/ds*(Fy_N - T(y))^2: curvature and gradient w.r.t. this stage (its Gauss-Newton
+        // part enters the Riccati recursion through the lifted variable, see k_step)
+        const double kT = -2.0 * (sf * pr.c.w_switch_F / ds) * (yn[QFY] - T.v);
+        hab += kT * T.ab;
+        rda += kT * T.a;
+        ga += kT * T.a;
+        if (diag) ab[5 * 8 + ia] = T.a;
+        if (q == 0) ab[6 * 8] = T.v;
+    }
+    if (diag && va < 8) rda += ws.at(b, W_LAM, k)[va];
+    ws.at(b, W_HC, k)[q] = hab;
+    if (diag) {
+        ws.at(b, W_RD, k)[va] = rda;
+        ws.at(b, W_GF, k)[va] = ga;
+        ws.at(b, W_V1, k)[va] = v1;
+        ws.at(b, W_V2, k)[va] = v2;
+    }
+    if (q == 0) {
+        double* cres = ws.at(b, W_CRES, k);
+#pragma unroll
+        for (int j = 0; j < NI_ST; ++j) cres[j] = ineq[j].v;
+        ws.at(b, W_FST, k)[0] = cost.v;
+        if (k == 0) {
+            double* g0 = ws.at(b, W_GRES, 0);
+            for (int i = 0; i < 8; ++i) g0[i] = yv[i] - pr.x0[(size_t)b * 8 + i];
+        }
+    }
+}
+
+// k_eval_pm: same for the PointMass stages (5 active variables -> 15 pairs).
+__global__ void __launch_bounds__(128) k_eval_pm(Prob pr, Ws ws) {
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const int M = pr.M, N = pr.N, H = pr.H;
+    if (t >= (long long)pr.B * M * 15) return;
+    const int q = (int)(t % 15), k = N + (int)((t / 15) % M), b = (int)(t / (15LL * M));
+    const double* sc = ws.scal(b);
+    if (sc[S_MODE] == MODE_DONE) return;
+    int ia, ib;
+    pair_from_index(q, ia, ib);
+    const int va = c_act_pm[ia], vb = c_act_pm[ib];
+    const bool diag = ia == ib;
+    const double* yv = ws.at(b, W_Y, k);
+    HDual y[7];
+#pragma unroll
+    for (int i = 0; i < 7; ++i) y[i] = HDual{yv[i], i == va ? 1.0 : 0.0, i == vb ? 1.0 : 0.0, 0.0};
+    const double sf = sc[S_SF];
+    const double kap = pr.kappa[(size_t)b * H + k], ds = pr.ds[(size_t)b * H + k];
+    HDual cost, ineq[NI_PM];
+    pm_cost_ineq(pr.p, pr.c, y, ds, k == H - 1, cost, ineq);
+    const double *z = ws.at(b, W_Z, k), *s = ws.at(b, W_S, k);
+    double hab = sf * cost.ab, ga = sf * cost.a, rda = ga, v1 = 0.0, v2 = 0.0;
+    double* jc = ws.at(b, W_JC, k);
+#pragma unroll
+    for (int j = 0; j < NI_PM; ++j) {
+        const double zj = z[j], is = 1.0 / s[j];
+        hab += -zj * ineq[j].ab + zj * is * ineq[j].a * ineq[j].b;
+        rda -= zj * ineq[j].a;
+        v1 += ineq[j].a * is;
+        v2 += ineq[j].a * zj * ineq[j].v * is;
+        if (diag) jc[j * 8 + ia] = ineq[j].a;
+    }
+    if (k < H - 1) {
+        HDual xn[5];
+        pm_euler<true>(pr.p, y, y + 5, kap, ds, xn);
+        const double* lam = ws.at(b, W_LAM, k + 1);
+        const double* yn = ws.at(b, W_Y, k + 1);
+        double* gres = ws.at(b, W_GRES, k + 1);
+        double* ab = ws.at(b, W_AB, k);
+#pragma unroll
+        for (int i = 0; i < 5; ++i) {
+            hab -= lam[i] * xn[i].ab;
+            rda -= lam[i] * xn[i].a;
+            if (diag) ab[i * 8 + ia] = xn[i].a;
+            if (q == 0) gres[i] = yn[i] - xn[i].v;
+        }
+    }
+    if (diag && va < 5) rda += ws.at(b, W_LAM, k)[va];
+    ws.at(b, W_HC, k)[q] = hab;
+    if (diag) {
+        ws.at(b, W_RD, k)[va] = rda;
+        ws.at(b, W_GF, k)[va] = ga;
+        ws.at(b, W_V1, k)[va] = v1;
+        ws.at(b, W_V2, k)[va] = v2;
+    }
+    if (q == 0) {
+        double* cres = ws.at(b, W_CRES, k);
+        cres[0] = ineq[0].v; cres[1] = ineq[1].v;
+        ws.at(b, W_FST, k)[0] = cost.v;
+        if (N == 0 && k == 0) {   // pure PointMass controller (not used by the shipped configs)
+            double* g0 = ws.at(b, W_GRES, 0);
+            for (int i = 0; i < 5; ++i) g0[i] = yv[i] - pr.x0[(size_t)b * 8 + i];
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// warp helpers
+#define FULL 0xffffffffu
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+    return v;
+}
+__device__ __forceinline__ double warp_max(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(FULL, v, o));
+    return v;
+}
+__device__ __forceinline__ double warp_min(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmin(v, __shfl_xor_sync(FULL, v, o));
+    return v;
+}
+// NaN-propagating max (fmax drops NaNs; evaluation errors must not be hidden)
+__device__ __forceinline__ double nmax(double a, double b) { return (a != a || b != b) ? NAN : fmax(a, b); }
+__device__ __forceinline__ double warp_nmax(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = nmax(v, __shfl_xor_sync(FULL, v, o));
+    return v;
+}
+
+// stage geometry ---------------------------------------------------------------------------------
+struct Dims { int nx, np, n, nu_off; bool st; };
+__device__ __forceinline__ Dims stage_dims(int N, int k) {
+    Dims d;
+    d.st = k < N;
+    d.nx = d.st ? 8 : 5;
+    d.np = k == 0 ? 0 : (d.st ? 1 : 2);
+    d.n = d.nx + d.np;
+    d.nu_off = d.st ? 8 : 5;   // index of the first control inside the stage variable vector y
+    return d;
+}
+// weights of the control-continuity terms between stage k and k+1 (unscaled): (c0 on Fx, c1 on Fy)
+//   cascaded_mpc.py:167-171 (SingleTrack), :228-231 (PointMass), :241-254 (switching; c1 ties Fy_N to Fy_f+Fy_r)
+__device__ __forceinline__ void slew_weights(const Prob& pr, const double* dsb, int k, double& c0, double& c1) {
+    c0 = c1 = 0.0;
+    if (k < 0 || k >= pr.H - 1) return;
+    const double ids = 1.0 / dsb[k];
+    if (k < pr.N - 1) c0 = pr.c.w_Fx * ids;
+    else if (k == pr.N - 1) { c0 = pr.c.w_switch_F * ids; c1 = c0; }
+    else { c0 = pr.c.w_Fx * ids; c1 = pr.c.w_Fy * ids; }
+}
+// previous-stage value that control j of stage k+1 is tied to
+__device__ __forceinline__ double slew_prev(const Prob& pr, const Ws& ws, int b, int k, int j, const double* yk) {
+    if (k == pr.N - 1 && pr.M > 0 && j == 1) return ws.at(b, W_AB, k)[6 * 8];   // T = Fy_f + Fy_r (from k_eval_st)
+    return yk[(k < pr.N ? 8 : 5) + j];
+}
+
+// Values of one stage at a trial point (plain doubles): objective share, constraint violation share,
+// log-barrier share.  y = stage variables, yn = next stage's (nullptr at the last stage), sl = trial slacks.
+struct StageVal { double f, theta, lns, gmax, cmin; };
+__device__ StageVal stage_trial(const Prob& pr, int b, int k, const double* y, const double* yn, const double* sl) {
+    StageVal o{0.0, 0.0, 0.0, 0.0, INFINITY};
+    const int H = pr.H, N = pr.N;
+    const double kap = pr.kappa[(size_t)b * H + k];
+    const double* dsb = pr.ds + (size_t)b * H;
+    const double ds = dsb[k];
+    double c0, c1;
+    slew_weights(pr, dsb, k, c0, c1);
+    if (k < N) {
+        double cost, ineq[NI_ST];
+        st_cost_ineq(pr.p, pr.c, y, ds, k == N - 1 && pr.M == 0, cost, ineq);
+        o.f = cost;
+#pragma unroll
+        for (int j = 0; j < NI_ST; ++j) { o.theta += fabs(ineq[j] - sl[j]); o.lns += log(sl[j]); o.cmin = fmin(o.cmin, ineq[j]); }
+        if (k == 0)
+            for (int i = 0; i < 8; ++i) { const double e = fabs(y[i] - pr.x0[(size_t)b * 8 + i]); o.theta += e; o.gmax = nmax(o.gmax, e); }
+        if (k < N - 1) {
+            double xn[8];
+            st_rk4<true>(pr.p, y, y + 8, kap, ds, xn);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) { const double e = fabs(yn[i] - xn[i]); o.theta += e; o.gmax = nmax(o.gmax, e); }
+            o.f += c0 * sq(yn[8] - y[8]);
+        } else if (pr.M > 0) {
+            double xp[5], T;
+            st_switch(pr.p, y, xp, T);
+#pragma unroll
+            for (int i = 0; i < 5; ++i) { const double e = fabs(yn[i] - xp[i]); o.theta += e; o.gmax = nmax(o.gmax, e); }
+            o.f += c0 * (sq(yn[QFX] - y[8]) + sq(yn[QFY] - T));
+        }
+        if (pr.c.obstacles && pr.n_obs > 0)
+            o.f += obstacle_cost(pr.obst + (size_t)b * pr.n_obs * 3, pr.n_obs, pr.c.w_obstacles, ds, y[IS], y[IEY],
+                                 nullptr, nullptr);
+        if (k == H - 1) o.f += pr.c.w_time * y[IT];
+    } else {
+        double cost, ineq[NI_PM];
+        pm_cost_ineq(pr.p, pr.c, y, ds, k == H - 1, cost, ineq);
+        o.f = cost;
+        for (int j = 0; j < NI_PM; ++j) { o.theta += fabs(ineq[j] - sl[j]); o.lns += log(sl[j]); o.cmin = fmin(o.cmin, ineq[j]); }
+        if (k < H - 1) {
+            double xn[5];
+            pm_euler<true>(pr.p, y, y + 5, kap, ds, xn);
+#pragma unroll
+            for (int i = 0; i < 5; ++i) { const double e = fabs(yn[i] - xn[i]); o.theta += e; o.gmax = nmax(o.gmax, e); }
+            o.f += c0 * sq(yn[QFX] - y[QFX]) + c1 * sq(yn[QFY] - y[QFY]);
+        }
+        if (pr.c.obstacles && pr.n_obs > 0)
+            o.f += obstacle_cost(pr.obst + (size_t)b * pr.n_obs * 3, pr.n_obs, pr.c.w_obstacles, ds, y[QS], y[QEY],
+                                 nullptr, nullptr);
+        if (k == H - 1) o.f += pr.c.w_time * y[QT];
+    }
+    return o;
+}
+
+// ------------------------------------------------------------------------------------------------
+// k_step building blocks (one warp per instance; `lane` strides over stages or matrix entries)
+constexpr int STEP_WARPS = 4;
+struct WarpSm {
+    double P[100];     // cost-to-go Hessian of the NEXT stage (stride 10)
+    double M[120];     // [A~ B~] of the lifted transition (stride 12)
+    double PMm[120];   // P * M
+    double G[144];     // stage Hessian + M^T P M (stride 12), order [x | p | u]
+    double p[12], r[12], g[12], x[12], tv[12], K[24];
+};
+
+struct Measures { double rdmax, prim, sumlam, sumz, theta, f, lns, gfmax; };
+
+// IPOPT options the reference leaves at their defaults (cascaded_mpc.py:55-65)
+struct IpmConst {
+    static constexpr double kappa_eps = 10.0, kappa_mu = 0.2, theta_mu = 1.5, tau_min = 0.99, slack_push = 1e-3,
+        kappa_sigma = 1e10, s_max = 100.0, gamma_theta = 1e-5, gamma_phi = 1e-8, eta_phi = 1e-8, delta = 1.0,
+        s_theta = 1.1, s_phi = 2.3, max_gradient = 100.0;
+};
+
+// completes the gradients that k_eval left open (s, t, obstacle and control-continuity parts) and reduces
+// the error measures over the warp
+__device__ Measures finish_gradients(const Prob& pr, const Ws& ws, int b, int lane) {
+    const int H = pr.H, N = pr.N;
+    const double* sc = ws.scal(b);
+    const double sf = sc[S_SF];
+    const double* dsb = pr.ds + (size_t)b * H;
+    Measures m{0, 0, 0, 0, 0, 0, 0, 0};
+    for (int k = lane; k < H; k += 32) {
+        const Dims d = stage_dims(N, k);
+        const double* y = ws.at(b, W_Y, k);
+        const int si = d.st ? IS : QS, ti = d.st ? IT : QT, eyi = d.st ? IEY : QEY;
+        double og[2] = {0, 0}, oh[3] = {0, 0, 0}, ov = 0.0;
+        if (pr.c.obstacles && pr.n_obs > 0)
+            ov = obstacle_cost(pr.obst + (size_t)b * pr.n_obs * 3, pr.n_obs, pr.c.w_obstacles, dsb[k], y[si], y[eyi], og, oh);
+        double* ob = ws.at(b, W_OBS, k);
+        ob[0] = ov; ob[1] = og[0]; ob[2] = og[1]; ob[3] = oh[0]; ob[4] = oh[1]; ob[5] = oh[2];
+        double p0, p1, c0, c1, g0 = 0.0, g1 = 0.0, fsl = 0.0;
+        slew_weights(pr, dsb, k - 1, p0, p1);
+        slew_weights(pr, dsb, k, c0, c1);
+        const double u0 = y[d.nu_off], u1 = y[d.nu_off + 1];
+        if (k > 0) {
+            const double* yp = ws.at(b, W_Y, k - 1);
+            g0 += 2.0 * p0 * (u0 - slew_prev(pr, ws, b, k - 1, 0, yp));
+            g1 += 2.0 * p1 * (u1 - slew_prev(pr, ws, b, k - 1, 1, yp));
+        }
+        double *rd = ws.at(b, W_RD, k), *gf = ws.at(b, W_GF, k), *v1 = ws.at(b, W_V1, k), *v2 = ws.at(b, W_V2, k);
+        const double* lam = ws.at(b, W_LAM, k);
+        double lam_s_next = 0.0, lam_t_next = 0.0;
+        if (k < H - 1) {
+            const Dims dn = stage_dims(N, k + 1);
+            const double* yn = ws.at(b, W_Y, k + 1);
+            const double e0 = yn[dn.nu_off] - u0;
+            g0 -= 2.0 * c0 * e0;
+            fsl += c0 * e0 * e0;
+            if (k == N - 1) {   // switching: Fy_N is tied to T(y_{N-1}); that gradient was taken by k_eval_st
+                const double e1 = yn[QFY] - slew_prev(pr, ws, b, k, 1, y);
+                fsl += c1 * e1 * e1;
+            } else {
+                const double e1 = yn[dn.nu_off + 1] - u1;
+                g1 -= 2.0 * c1 * e1;
+                fsl += c1 * e1 * e1;
+            }
+            const double* ln = ws.at(b, W_LAM, k + 1);
+            lam_s_next = ln[dn.st ? IS : QS];
+            lam_t_next = ln[dn.st ? IT : QT];
+        }
+        const double wt = (k == H - 1) ? sf * pr.c.w_time : 0.0;
+        rd[d.nu_off] += sf * g0; gf[d.nu_off] += sf * g0;
+        rd[d.nu_off + 1] += sf * g1; gf[d.nu_off + 1] += sf * g1;
+        rd[si] = lam[si] - lam_s_next + sf * og[0]; gf[si] = sf * og[0];
+        rd[ti] = lam[ti] - lam_t_next + wt; gf[ti] = wt;
+        rd[eyi] += sf * og[1]; gf[eyi] += sf * og[1];
+        v1[si] = v1[ti] = v2[si] = v2[ti] = 0.0;
+        for (int i = 0; i < d.nx + 2; ++i) { m.rdmax = nmax(m.rdmax, fabs(rd[i])); m.gfmax = nmax(m.gfmax, fabs(gf[i])); }
+        const double* gr = ws.at(b, W_GRES, k);
+        for (int i = 0; i < d.nx; ++i) { m.prim = nmax(m.prim, fabs(gr[i])); m.theta += fabs(gr[i]); m.sumlam += fabs(lam[i]); }
+        const double *cr = ws.at(b, W_CRES, k), *s = ws.at(b, W_S, k), *z = ws.at(b, W_Z, k);
+        for (int j = 0; j < (d.st ? NI_ST : NI_PM); ++j) {
+            const double r = cr[j] - s[j];
+            m.prim = nmax(m.prim, fabs(r)); m.theta += fabs(r); m.sumz += fabs(z[j]); m.lns += log(s[j]);
+        }
+        m.f += ws.at(b, W_FST, k)[0] + ov + fsl + (k == H - 1 ? pr.c.w_time * y[ti] : 0.0);
+    }
+    m.rdmax = warp_nmax(m.rdmax); m.gfmax = warp_nmax(m.gfmax); m.prim = warp_nmax(m.prim);
+    m.sumlam = warp_sum(m.sumlam); m.sumz = warp_sum(m.sumz); m.theta = warp_sum(m.theta);
+    m.f = warp_sum(m.f); m.lns = warp_sum(m.lns);
+    return m;
+}
+
+__device__ double compl_error(const Prob& pr, const Ws& ws, int b, int lane, double mu) {
+    double e = 0.0;
+    for (int k = lane; k < pr.H; k += 32) {
+        const double *s = ws.at(b, W_S, k), *z = ws.at(b, W_Z, k);
+        for (int j = 0; j < (k < pr.N ? NI_ST : NI_PM); ++j) e = fmax(e, fabs(s[j] * z[j] - mu));
+    }
+    return warp_max(e);
+}
+
+// slack / multiplier initialisation (IPOPT warm_start_*_bound_push 1e-3; oracle/ipm.py)
+__device__ void init_slacks(const Prob& pr, const Ws& ws, int b, int lane, double mu) {
+    for (int k = lane; k < pr.H; k += 32) {
+        const double* cr = ws.at(b, W_CRES, k);
+        double *s = ws.at(b, W_S, k), *z = ws.at(b, W_Z, k), *lam = ws.at(b, W_LAM, k);
+        for (int j = 0; j < (k < pr.N ? NI_ST : NI_PM); ++j) {
+            s[j] = fmax(cr[j], IpmConst::slack_push * fmax(1.0, fabs(cr[j])));
+            z[j] = mu / s[j];
+        }
+        for (int i = 0; i < 8; ++i) lam[i] = 0.0;
+    }
+}
+
+// writes the result of a finished instance back in the reference's layout
+__device__ void finalize(const Prob& pr, const Ws& ws, int b, int lane, int status, double obj, double err) {
+    const int H = pr.H;
+    double* Xb = pr.X + (size_t)b * 8 * H;
+    double* Ub = pr.U + (size_t)b * 2 * H;
+    for (int k = lane; k < H; k += 32) {
+        const double* y = ws.at(b, W_Y, k);
+        if (k < pr.N) {
+            for (int i = 0; i < 8; ++i) Xb[i * H + k] = y[i];
+            Ub[k] = y[8]; Ub[H + k] = y[9];
+        } else {
+            for (int i = 0; i < 5; ++i) Xb[i * H + k] = y[i];   // rows 5..7 of PointMass columns are free variables
+            Ub[k] = y[5]; Ub[H + k] = y[6];
+        }
+    }
+    if (lane == 0) {
+        double* sc = ws.scal(b);
+        sc[S_MODE] = MODE_DONE; sc[S_STATUS] = status; sc[S_OBJ] = obj; sc[S_ERR] = err;
+        if (pr.obj) pr.obj[b] = obj;
+        if (pr.kkt) pr.kkt[b] = err;
+        if (pr.status) pr.status[b] = status;
+        if (pr.iters) pr.iters[b] = (int)sc[S_ITERS];
+    }
+}
+
+// position of stage variable i of stage k inside the Riccati ordering [x | p | u]
+__device__ __forceinline__ int gpos(const Dims& d, int i) { return i < d.nu_off ? i : d.n + (i - d.nu_off); }
+
+// builds M = [A~ B~] (rows: lifted next state, cols: [x | p | u] of stage k) and r~ in shared memory
+__device__ void build_transition(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int lane, int k, const Dims& d,
+                                 const Dims& dn) {
+    const int nn = d.n + 2;
+    for (int e = lane; e < dn.n * 12; e += 32) sm.M[e] = 0.0;
+    __syncwarp();
+    const double* ab = ws.at(b, W_AB, k);
+    const int na = d.st ? 8 : 5;
+    for (int e = lane; e < dn.nx * na; e += 32) {
+        const int i = e / na, a = e % na;
+        const int yi = d.st ? c_act_st[a] : c_act_pm[a];
+        sm.M[i * 12 + gpos(d, yi)] = ab[i * 8 + a];
+    }
+    if (lane == 0) {   // s and t pass through with unit derivative
+        sm.M[(dn.st ? IS : QS) * 12 + (d.st ? IS : QS)] = 1.0;
+        sm.M[(dn.st ? IT : QT) * 12 + (d.st ? IT : QT)] = 1.0;
+        sm.M[dn.nx * 12 + d.n] = 1.0;                              // p0 <- Fx_k
+        if (dn.np > 1 && !d.st) sm.M[(dn.nx + 1) * 12 + d.n + 1] = 1.0;   // p1 <- Fy_k
+    }
+    if (dn.np > 1 && d.st && lane < 8)                             // p1 <- T(y_{N-1}) = Fy_f + Fy_r
+        sm.M[(dn.nx + 1) * 12 + gpos(d, c_act_st[lane])] = ab[5 * 8 + lane];
+    if (lane < dn.n) sm.r[lane] = lane < dn.nx ? -ws.at(b, W_GRES, k + 1)[lane] : 0.0;
+    (void)nn;
+    __syncwarp();
+}
+
+// Backward Riccati sweep + forward substitution of the condensed KKT system
+//   [Hc + delta I  Jg^T] [dw  ]   [-(rd - mu v1 + v2)]
+//   [Jg            0   ] [dlam] = [-g                ]
+// Returns false when some reduced Hessian block is not positive definite (wrong inertia for this delta).
+__device__ bool riccati(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int lane, double mu, double delta) {
+    const int H = pr.H, N = pr.N;
+    const double sf = ws.scal(b)[S_SF];
+    const double* dsb = pr.ds + (size_t)b * H;
+    bool ok = true;
+    for (int k = H - 1; k >= 0 && ok; --k) {
+        const Dims d = stage_dims(N, k);
+        const int n = d.n, nn = n + 2;
+        for (int e = lane; e < 144; e += 32) sm.G[e] = 0.0;
+        __syncwarp();
+        {   // stage Hessian block over the active variables
+            const double* hc = ws.at(b, W_HC, k);
+            const int npair = d.st ? 36 : 15;
+            for (int q = lane; q < npair; q += 32) {
+                int ia, ib;
+                pair_from_index(q, ia, ib);
+                const int pa = gpos(d, d.st ? c_act_st[ia] : c_act_pm[ia]), pb = gpos(d, d.st ? c_act_st[ib] : c_act_pm[ib]);
+                const double v = hc[q];
+                sm.G[pa * 12 + pb] = v;
+                sm.G[pb * 12 + pa] = v;
+            }
+            const double *rd = ws.at(b, W_RD, k), *v1 = ws.at(b, W_V1, k), *v2 = ws.at(b, W_V2, k);
+            if (lane < d.nx + 2) sm.g[gpos(d, lane)] = rd[lane] - mu * v1[lane] + v2[lane];
+            if (lane >= d.nx && lane < n) sm.g[lane] = 0.0;   // lifted variables carry no linear term
+        }
+        __syncwarp();
+        if (lane == 0) {
+            const double* ob = ws.at(b, W_OBS, k);
+            const int si = d.st ? IS : QS, eyi = d.st ? IEY : QEY;
+            sm.G[si * 12 + si] += sf * ob[3];
+            sm.G[si * 12 + eyi] += sf * ob[4];
+            sm.G[eyi * 12 + si] += sf * ob[4];
+            sm.G[eyi * 12 + eyi] += sf * ob[5];
+            double p0, p1;
+            slew_weights(pr, dsb, k - 1, p0, p1);
+            const double cc[2] = {2.0 * sf * p0, 2.0 * sf * p1};
+            for (int j = 0; j < d.np; ++j) {
+                sm.G[(n + j) * 12 + n + j] += cc[j];
+                sm.G[(d.nx + j) * 12 + d.nx + j] += cc[j];
+                sm.G[(n + j) * 12 + d.nx + j] -= cc[j];
+                sm.G[(d.nx + j) * 12 + n + j] -= cc[j];
+            }
+            for (int i = 0; i < d.nx; ++i) sm.G[i * 12 + i] += delta;
+            sm.G[n * 12 + n] += delta;
+            sm.G[(n + 1) * 12 + n + 1] += delta;
+        }
+        __syncwarp();
+        if (k < H - 1) {
+            const Dims dn = stage_dims(N, k + 1);
+            build_transition(pr, ws, sm, b, lane, k, d, dn);
+            for (int e = lane; e < dn.n * nn; e += 32) {      // PMm = P M
+                const int i = e / nn, j = e % nn;
+                double a = 0.0;
+                for (int l = 0; l < dn.n; ++l) a += sm.P[i * 10 + l] * sm.M[l * 12 + j];
+                sm.PMm[i * 12 + j] = a;
+            }
+            if (lane < dn.n) {                                 // tv = P r + p
+                double a = sm.p[lane];
+                for (int l = 0; l < dn.n; ++l) a += sm.P[lane * 10 + l] * sm.r[l];
+                sm.tv[lane] = a;
+            }
+            __syncwarp();
+            for (int e = lane; e < nn * nn; e += 32) {         // G += M^T (P M)
+                const int i = e / nn, j = e % nn;
+                double a = 0.0;
+                for (int l = 0; l < dn.n; ++l) a += sm.M[l * 12 + i] * sm.PMm[l * 12 + j];
+                sm.G[i * 12 + j] += a;
+            }
+            if (lane < nn) {                                   // g += M^T tv
+                double a = 0.0;
+                for (int l = 0; l < dn.n; ++l) a += sm.M[l * 12 + lane] * sm.tv[l];
+                sm.g[lane] += a;
+            }
+            __syncwarp();
+        }
+        // reduced Hessian of the two controls
+        const double ra = sm.G[n * 12 + n], rb = 0.5 * (sm.G[n * 12 + n + 1] + sm.G[(n + 1) * 12 + n]),
+                     rdd = sm.G[(n + 1) * 12 + n + 1];
+        const double det = ra * rdd - rb * rb;
+        if (!(ra > 0.0) || !(det > 0.0) || !isfinite(det)) { ok = false; break; }
+        const double i00 = rdd / det, i01 = -rb / det, i11 = ra / det;
+        double* km = ws.at(b, W_KM, k);
+        if (lane < n) {
+            const double g0 = sm.G[n * 12 + lane], g1 = sm.G[(n + 1) * 12 + lane];
+            const double k0 = -(i00 * g0 + i01 * g1), k1 = -(i01 * g0 + i11 * g1);
+            sm.K[lane] = k0; sm.K[12 + lane] = k1;
+            km[lane] = k0; km[10 + lane] = k1;
+        }
+        if (lane == 31) {
+            const double g0 = sm.g[n], g1 = sm.g[n + 1];
+            const double f0 = -(i00 * g0 + i01 * g1), f1 = -(i01 * g0 + i11 * g1);
+            sm.K[10] = f0; sm.K[22] = f1;
+            km[20] = f0; km[21] = f1;
+        }
+        __syncwarp();
+        double* pm = ws.at(b, W_PM, k);
+        double* pv = ws.at(b, W_PV, k);
+        for (int e = lane; e < n * n; e += 32) {               // P = Gxx + Gxu K   (symmetrised)
+            const int i = e / n, j = e % n;
+            const double a = sm.G[i * 12 + j] + sm.G[i * 12 + n] * sm.K[j] + sm.G[i * 12 + n + 1] * sm.K[12 + j];
+            const double c = sm.G[j * 12 + i] + sm.G[j * 12 + n] * sm.K[i] + sm.G[j * 12 + n + 1] * sm.K[12 + i];
+            const double v = 0.5 * (a + c);
+            sm.P[i * 10 + j] = v;
+            pm[i * 10 + j] = v;
+        }
+        if (lane < n) {
+            const double v = sm.g[lane] + sm.G[lane * 12 + n] * sm.K[10] + sm.G[lane * 12 + n + 1] * sm.K[22];
+            sm.p[lane] = v;
+            pv[lane] = v;
+        }
+        __syncwarp();
+    }
+    if (!ok) return false;
+    // ---- forward substitution
+    if (lane < 12) sm.x[lane] = lane < 8 ? -ws.at(b, W_GRES, 0)[lane] : 0.0;
+    __syncwarp();
+    for (int k = 0; k < H; ++k) {
+        const Dims d = stage_dims(N, k);
+        const int n = d.n;
+        const double* km = ws.at(b, W_KM, k);
+        if (lane < 2) {
+            double a = km[20 + lane];
+            for (int l = 0; l < n; ++l) a += km[lane * 10 + l] * sm.x[l];
+            sm.x[n + lane] = a;
+        }
+        __syncwarp();
+        double* dy = ws.at(b, W_DY, k);
+        if (lane < d.nx) {
+            dy[lane] = sm.x[lane];
+            const double* pm = ws.at(b, W_PM, k);
+            double a = ws.at(b, W_PV, k)[lane];
+            for (int l = 0; l < n; ++l) a += pm[lane * 10 + l] * sm.x[l];
+            ws.at(b, W_DLAM, k)[lane] = -a;
+        }
+        if (lane < 2) dy[d.nu_off + lane] = sm.x[n + lane];
+        if (k < H - 1) {
+            const Dims dn = stage_dims(N, k + 1);
+            build_transition(pr, ws, sm, b, lane, k, d, dn);
+            double a = 0.0;
+            if (lane < dn.n) {
+                a = sm.r[lane];
+                for (int l = 0; l < n + 2; ++l) a += sm.M[lane * 12 + l] * sm.x[l];
+            }
+            __syncwarp();
+            if (lane < dn.n) sm.x[lane] = a;
+            __syncwarp();
+        }
+    }
+    return true;
+}
+
+// restoration substitute (oracle/nlp.py NLP.repair): clip the steering rate, roll the models out from x0
+__device__ void repair_rollout(const Prob& pr, const Ws& ws, int b) {
+    const int H = pr.H, N = pr.N;
+    const double* kap = pr.kappa + (size_t)b * H;
+    const double* dsb = pr.ds + (size_t)b * H;
+    double* y = ws.at(b, W_Y, 0);
+    for (int i = 0; i < 8; ++i) y[i] = pr.x0[(size_t)b * 8 + i];
+    for (int k = 0; k < N; ++k) {
+        y = ws.at(b, W_Y, k);
+        y[YW] = fmin(fmax(y[YW], pr.c.w_min), pr.c.w_max);
+        if (k < N - 1) st_rk4<true>(pr.p, y, y + 8, kap[k], dsb[k], ws.at(b, W_Y, k + 1));
+    }
+    if (pr.M > 0) {
+        double T;
+        st_switch(pr.p, ws.at(b, W_Y, N - 1), ws.at(b, W_Y, N), T);
+        for (int k = N; k < H - 1; ++k) {
+            y = ws.at(b, W_Y, k);
+            pm_euler<true>(pr.p, y, y + 5, kap[k], dsb[k], ws.at(b, W_Y, k + 1));
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// k_step: one interior-point iteration of every unfinished instance (one warp each)
+__global__ void __launch_bounds__(32 * STEP_WARPS) k_step(Prob pr, Ws ws, int* n_active) {
+    __shared__ WarpSm s_all[STEP_WARPS];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int b = blockIdx.x * STEP_WARPS + wid;
+    if (b >= pr.B) return;
+    WarpSm& sm = s_all[wid];
+    double* sc = ws.scal(b);
+    const int mode = (int)sc[S_MODE];
+    if (mode == MODE_DONE) return;
+    if (lane == 0) atomicAdd(n_active, 1);
+    const int H = pr.H, N = pr.N, M = pr.M;
+    const Cfg& c = pr.c;
+    const Measures m = finish_gradients(pr, ws, b, lane);
+    const bool finite = isfinite(m.f) && isfinite(m.theta) && isfinite(m.rdmax) && isfinite(m.prim);
+    double mu = sc[S_MU];
+    const double sf = sc[S_SF];
+    if (mode == MODE_INIT || mode == MODE_REINIT) {
+        if (!finite) { finalize(pr, ws, b, lane, VC_EVAL_ERROR, m.f, INFINITY); return; }
+        if (mode == MODE_INIT && c.obj_scaling && m.gfmax > IpmConst::max_gradient && lane == 0)
+            sc[S_SF] = IpmConst::max_gradient / m.gfmax;   // gradient-based objective scaling at the initial point
+        init_slacks(pr, ws, b, lane, mu);
+        if (lane == 0) { sc[S_MODE] = MODE_STEP; sc[S_NFILT] = 0; sc[S_THETA0] = -1.0; sc[S_ACC] = 0; }
+        return;
+    }
+    // ---- convergence test (IPOPT overall error E_0) and barrier update
+    const int me = 8 + 8 * (N - 1) + (M > 0 ? 5 * M : 0), mi = NI_ST * N + NI_PM * M;
+    const double sd = fmax(IpmConst::s_max, (m.sumlam + m.sumz) / (me + mi)) / IpmConst::s_max;
+    const double scs = fmax(IpmConst::s_max, m.sumz / mi) / IpmConst::s_max;
+    const double e_dp = fmax(m.rdmax / sd, m.prim);
+    const double err0 = fmax(e_dp, compl_error(pr, ws, b, lane, 0.0) / scs);
+    const double obj = m.f;
+    int iters = (int)sc[S_ITERS];
+    if (!finite) { finalize(pr, ws, b, lane, VC_EVAL_ERROR, obj, INFINITY); return; }
+    if (err0 <= c.tol) { finalize(pr, ws, b, lane, VC_SOLVED, obj, err0); return; }
+    int acc = (err0 <= c.acceptable_tol) ? (int)sc[S_ACC] + 1 : 0;
+    if (acc >= c.acceptable_iter) { finalize(pr, ws, b, lane, VC_ACCEPTABLE, obj, err0); return; }
+    if (iters >= c.max_iter) { finalize(pr, ws, b, lane, VC_MAX_ITER, obj, err0); return; }
+    int nfilt = (int)sc[S_NFILT];
+    const double mu_floor = c.tol / 11.0;
+    while (mu > mu_floor * (1 + 1e-12) &&
+           fmax(e_dp, compl_error(pr, ws, b, lane, mu) / scs) <= IpmConst::kappa_eps * mu) {
+        mu = fmax(mu_floor, fmin(IpmConst::kappa_mu * mu, pow(mu, IpmConst::theta_mu)));
+        nfilt = 0;
+    }
+    const double tau = fmax(IpmConst::tau_min, 1.0 - mu);
+    const double theta = m.theta, phi = sf * m.f - mu * m.lns;
+    double theta0 = sc[S_THETA0];
+    if (theta0 < 0.0) theta0 = theta;
+    const double theta_min = 1e-4 * fmax(1.0, theta0), theta_max = 1e4 * fmax(1.0, theta0);
+    const double delta_last = sc[S_DELTA_LAST];
+    const bool first_ever = delta_last == 0.0;
+    double trial = 0.0, alpha = 0.0, a_d = 1.0;
+    bool accepted = false, failed = false;
+    double* filt_t = sc + S_FILT;
+    double* filt_p = sc + S_FILP;
+    while (!accepted && !failed) {
+        // ---- inertia-correcting factorisation (IPOPT delta_w ladder)
+        while (!riccati(pr, ws, sm, b, lane, mu, trial)) {
+            if (trial == 0.0) trial = first_ever ? 1e-4 : fmax(1e-20, delta_last / 3.0);
+            else trial *= first_ever ? 100.0 : 8.0;
+            if (trial > 1e40) { failed = true; break; }
+        }
+        if (failed) break;
+        // ---- slack / multiplier directions, fraction to the boundary, directional derivative
+        double a_p = 1.0, dphi = 0.0;
+        a_d = 1.0;
+        for (int k = lane; k < H; k += 32) {
+            const bool st = k < N;
+            const int na = st ? 8 : 5;
+            const double *jc = ws.at(b, W_JC, k), *dy = ws.at(b, W_DY, k), *cr = ws.at(b, W_CRES, k);
+            const double *s = ws.at(b, W_S, k), *z = ws.at(b, W_Z, k), *gf = ws.at(b, W_GF, k);
+            double *dsl = ws.at(b, W_DSL, k), *dz = ws.at(b, W_DZ, k);
+            for (int j = 0; j < (st ? NI_ST : NI_PM); ++j) {
+                double a = cr[j] - s[j];
+                for (int q = 0; q < na; ++q) a += jc[j * 8 + q] * dy[st ? c_act_st[q] : c_act_pm[q]];
+                const double dzj = mu / s[j] - z[j] - (z[j] / s[j]) * a;
+                dsl[j] = a; dz[j] = dzj;
+                if (a < 0.0) a_p = fmin(a_p, -tau * s[j] / a);
+                if (dzj < 0.0) a_d = fmin(a_d, -tau * z[j] / dzj);
+                dphi -= mu * a / s[j];
+            }
+            for (int i = 0; i < (st ? 10 : 7); ++i) dphi += gf[i] * dy[i];
+        }
+        a_p = warp_min(a_p); a_d = warp_min(a_d); dphi = warp_sum(dphi);
+        // ---- filter line search, lanes over stages
+        alpha = a_p;
+        for (int bt = 0; bt < 12 && !accepted; ++bt, alpha *= 0.5) {
+            double ft = 0.0, tht = 0.0, lnt = 0.0;
+            for (int k = lane; k < H; k += 32) {
+                double yt[10], yn[10], st_[10];
+                const int nv = k < N ? 10 : 7;
+                const double *y = ws.at(b, W_Y, k), *dy = ws.at(b, W_DY, k);
+                for (int i = 0; i < nv; ++i) yt[i] = y[i] + alpha * dy[i];
+                if (k < H - 1) {
+                    const double *y1 = ws.at(b, W_Y, k + 1), *dy1 = ws.at(b, W_DY, k + 1);
+                    for (int i = 0; i < (k + 1 < N ? 10 : 7); ++i) yn[i] = y1[i] + alpha * dy1[i];
+                }
+                const double *s = ws.at(b, W_S, k), *dsl = ws.at(b, W_DSL, k);
+                for (int j = 0; j < (k < N ? NI_ST : NI_PM); ++j) st_[j] = s[j] + alpha * dsl[j];
+                const StageVal v = stage_trial(pr, b, k, yt, yn, st_);
+                ft += v.f; tht += v.theta; lnt += v.lns;
+            }
+            ft = warp_sum(ft); tht = warp_sum(tht); lnt = warp_sum(lnt);
+            if (!(isfinite(ft) && isfinite(tht) && isfinite(lnt))) continue;   // evaluation error: backtrack
+            const double pht = sf * ft - mu * lnt;
+            bool in_filter = tht > theta_max;
+            for (int i = 0; i < nfilt; ++i) in_filter = in_filter || (tht >= filt_t[i] && pht >= filt_p[i]);
+            if (in_filter) continue;
+            const bool switching = theta <= theta_min && dphi < 0.0 &&
+                                   alpha * pow(-dphi, IpmConst::s_phi) > IpmConst::delta * pow(theta, IpmConst::s_theta);
+            bool augment = false;
+            if (switching) {
+                if (pht <= phi + IpmConst::eta_phi * alpha * dphi) accepted = true;
+            } else if (tht <= (1 - IpmConst::gamma_theta) * theta || pht <= phi - IpmConst::gamma_phi * theta) {
+                accepted = true; augment = true;
+            }
+            if (!accepted && fabs(pht - phi) <= 1e-13 * fmax(1.0, fabs(phi)) && tht <= theta + 1e-13) accepted = true;
+            if (accepted && augment) {
+                if (nfilt < FILT_MAX) {
+                    if (lane == 0) { filt_t[nfilt] = (1 - IpmConst::gamma_theta) * theta; filt_p[nfilt] = phi - IpmConst::gamma_phi * theta; }
+                    ++nfilt;
+                }
+            }
+            if (accepted) break;
+        }
+        __syncwarp();
+        if (accepted) break;
+        // no acceptable step along this direction: damp it (larger delta_w) and retry; IPOPT would restore here
+        trial = fmax(trial, 1e-4) * 100.0;
+        if (trial > 1e12) failed = true;
+    }
+    if (failed) {
+        const int restarts = (int)sc[S_RESTARTS];
+        if (restarts >= 2) { finalize(pr, ws, b, lane, VC_LINESEARCH_FAIL, obj, err0); return; }
+        __syncwarp();
+        if (lane == 0) {
+            repair_rollout(pr, ws, b);
+            sc[S_RESTARTS] = restarts + 1; sc[S_MODE] = MODE_REINIT; sc[S_MU] = c.mu_init; sc[S_DELTA_LAST] = 0.0;
+            sc[S_ITERS] = iters + 1;
+        }
+        for (int k = lane; k < H; k += 32) {   // neutral multipliers / slacks for the re-evaluation
+            double *lam = ws.at(b, W_LAM, k), *s = ws.at(b, W_S, k), *z = ws.at(b, W_Z, k);
+            for (int i = 0; i < 8; ++i) lam[i] = 0.0;
+            for (int j = 0; j < 10; ++j) { s[j] = 1.0; z[j] = 0.0; }
+        }
+        return;
+    }
+    // ---- accept: primal-dual update with the z safeguard (IPOPT kappa_sigma)
+    for (int k = lane; k < H; k += 32) {
+        const bool st = k < N;
+        double *y = ws.at(b, W_Y, k), *lam = ws.at(b, W_LAM, k), *s = ws.at(b, W_S, k), *z = ws.at(b, W_Z, k);
+        const double *dy = ws.at(b, W_DY, k), *dl = ws.at(b, W_DLAM, k), *dsl = ws.at(b, W_DSL, k), *dz = ws.at(b, W_DZ, k);
+        for (int i = 0; i < (st ? 10 : 7); ++i) y[i] += alpha * dy[i];
+        for (int i = 0; i < (st ? 8 : 5); ++i) lam[i] += alpha * dl[i];
+        for (int j = 0; j < (st ? NI_ST : NI_PM); ++j) {
+            s[j] += alpha * dsl[j];
+            double zj = z[j] + a_d * dz[j];
+            zj = fmin(fmax(zj, mu / (IpmConst::kappa_sigma * s[j])), IpmConst::kappa_sigma * mu / s[j]);
+            z[j] = zj;
+        }
+    }
+    if (lane == 0) {
+        sc[S_MU] = mu; sc[S_NFILT] = nfilt; sc[S_THETA0] = theta0; sc[S_ACC] = acc; sc[S_ITERS] = iters + 1;
+        if (trial > 0.0) sc[S_DELTA_LAST] = trial;
+        sc[S_OBJ] = obj; sc[S_ERR] = err0;
+    }
+}
+
+// k_nmpc_eval: objective / max equality violation / min inequality margin of given trajectories (no solve)
+__global__ void __launch_bounds__(128) k_nmpc_eval(Prob pr, const double* X, const double* U, double* out) {
+    const int lane = threadIdx.x & 31;
+    const int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (b >= pr.B) return;
+    const int H = pr.H, N = pr.N;
+    const double* Xb = X + (size_t)b * 8 * H;
+    const double* Ub = U + (size_t)b * 2 * H;
+    double f = 0.0, gmax = 0.0, cmin = INFINITY;
+    for (int k = lane; k < H; k += 32) {
+        double y[10], yn[10], sl[10];
+        for (int kk = k; kk <= k + 1 && kk < H; ++kk) {
+            double* d = kk == k ? y : yn;
+            const int nx = kk < N ? 8 : 5;
+            for (int i = 0; i < nx; ++i) d[i] = Xb[i * H + kk];
+            d[nx] = Ub[kk]; d[nx + 1] = Ub[H + kk];
+        }
+        for (int j = 0; j < 10; ++j) sl[j] = 1.0;
+        const StageVal v = stage_trial(pr, b, k, y, yn, sl);
+        f += v.f; gmax = nmax(gmax, v.gmax); cmin = fmin(cmin, v.cmin);
+    }
+    f = warp_sum(f); gmax = warp_nmax(gmax); cmin = warp_min(cmin);
+    if (lane == 0) { out[(size_t)b * 3] = f; out[(size_t)b * 3 + 1] = gmax; out[(size_t)b * 3 + 2] = cmin; }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+static int fill_prob(vc_handle* h, Prob& pr, int B, const double* d_x0, const double* d_kappa, const double* d_ds,
+                     const double* d_obst, int n_obs) {
+    if (h->cfg.N < 1 || h->cfg.M < 0) { set_error("nmpc: config not set (need horizon N >= 1, M >= 0)"); return -1; }
+    if (h->cfg.N + h->cfg.M > 4096) { set_error("nmpc: horizon too long"); return -1; }
+    if (!d_x0 || !d_kappa || !d_ds) { set_error("nmpc: null input pointer"); return -1; }
+    if (h->cfg.obstacles && n_obs > 0 && !d_obst) { set_error("nmpc: obstacles enabled but d_obst is null"); return -1; }
+    pr.p = h->params; pr.c = h->cfg;
+    pr.B = B; pr.N = h->cfg.N; pr.M = h->cfg.M; pr.H = pr.N + pr.M;
+    pr.n_obs = (h->cfg.obstacles && d_obst) ? n_obs : 0;
+    pr.x0 = d_x0; pr.kappa = d_kappa; pr.ds = d_ds; pr.obst = d_obst;
+    pr.X = pr.U = pr.obj = pr.kkt = nullptr; pr.status = pr.iters = nullptr;
+    return 0;
+}
+
+int launch_nmpc_eval(vc_handle* h, int B, const double* d_x0, const double* d_kappa, const double* d_ds,
+                     const double* d_obst, int n_obs, const double* d_X, const double* d_U, double* d_out) {
+    Prob pr;
+    int rc = fill_prob(h, pr, B, d_x0, d_kappa, d_ds, d_obst, n_obs);
+    if (rc) return rc;
+    cudaSetDevice(h->device);
+    const long long threads = (long long)B * 32;
+    k_nmpc_eval<<<(unsigned)((threads + 127) / 128), 128, 0, h->stream>>>(pr, d_X, d_U, d_out);
+    h->launches++;
+    return check_cuda(cudaGetLastError(), "k_nmpc_eval");
+}
+
+int launch_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_kappa, const double* d_ds,
+                      const double* d_obst, int n_obs, double* d_X, double* d_U, double* d_obj, int* d_status,
+                      int* d_iters, double* d_kkt) {
+    Prob pr;
+    int rc = fill_prob(h, pr, B, d_x0, d_kappa, d_ds, d_obst, n_obs);
+    if (rc) return rc;
+    if (!d_X || !d_U) { set_error("nmpc: null X/U pointer"); return -1; }
+    pr.X = d_X; pr.U = d_U; pr.obj = d_obj; pr.kkt = d_kkt; pr.status = d_status; pr.iters = d_iters;
+    cudaSetDevice(h->device);
+    Ws ws;
+    ws.H = pr.H;
+    ws.stride = (size_t)WS_PER_STAGE * pr.H + NSCAL;
+    const size_t bytes = ws.stride * sizeof(double) * (size_t)B;
+    if (bytes > h->ws_bytes) {
+        cudaFree(h->d_ws);
+        h->d_ws = nullptr; h->ws_bytes = 0;
+        rc = check_cuda(cudaMalloc(&h->d_ws, bytes), "cudaMalloc(nmpc workspace)");
+        if (rc) return rc;
+        h->ws_bytes = bytes;
+    }
+    if (!h->d_active) {
+        rc = check_cuda(cudaMalloc(&h->d_active, sizeof(int)), "cudaMalloc(active)");
+        if (rc) return rc;
+        rc = check_cuda(cudaMallocHost(&h->h_active, sizeof(int)), "cudaMallocHost(active)");
+        if (rc) return rc;
+    }
+    ws.base = (double*)h->d_ws;
+    cudaStream_t st = h->stream;
+    k_prepare<<<(B * pr.H + 127) / 128, 128, 0, st>>>(pr, ws);
+    h->launches++;
+    const long long t_st = (long long)B * pr.N * 36, t_pm = (long long)B * pr.M * 15;
+    const int max_pass = h->cfg.max_iter + 16;
+    const bool debug = getenv("VC_DEBUG") != nullptr;
+    int pass = 0;
+    for (; pass < max_pass; ++pass) {
+        k_eval_st<<<(unsigned)((t_st + 127) / 128), 128, 0, st>>>(pr, ws);
+        if (pr.M > 0) k_eval_pm<<<(unsigned)((t_pm + 127) / 128), 128, 0, st>>>(pr, ws);
+        cudaMemsetAsync(h->d_active, 0, sizeof(int), st);
+        k_step<<<(B + STEP_WARPS - 1) / STEP_WARPS, 32 * STEP_WARPS, 0, st>>>(pr, ws, h->d_active);
+        h->launches += pr.M > 0 ? 3 : 2;
+        if (debug) {   // VC_DEBUG=1: trace instance 0
+            double sc[NSCAL];
+            cudaMemcpyAsync(sc, ws.scal(0), sizeof(sc), cudaMemcpyDeviceToHost, st);
+            cudaStreamSynchronize(st);
+            fprintf(stderr, "[vc] pass %3d mode %d it %3d mu %.3e sf %.4g obj %.10f err %.3e delta %.2e nfilt %d restarts %d status %d\n",
+                    pass, (int)sc[S_MODE], (int)sc[S_ITERS], sc[S_MU], sc[S_SF], sc[S_OBJ], sc[S_ERR], sc[S_DELTA_LAST],
+                    (int)sc[S_NFILT], (int)sc[S_RESTARTS], (int)sc[S_STATUS]);
+        }
+        if (pass >= 4) {   // finished instances idle; stop as soon as none is left
+            cudaMemcpyAsync(h->h_active, h->d_active, sizeof(int), cudaMemcpyDeviceToHost, st);
+            rc = check_cuda(cudaStreamSynchronize(st), "nmpc iteration");
+            if (rc) return rc;
+            if (*h->h_active == 0) break;
+        }
+    }
+    h->last_passes = pass + 1;
+    return check_cuda(cudaGetLastError(), "nmpc solve");
+}
+
+}  // namespace vc
