@@ -35,6 +35,7 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default=None, choices=["nmpc", "rollout"])
     ap.add_argument("--batch", type=int, default=0, help="instances per GPU (0 = config default)")
+    ap.add_argument("--e2e-batch", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
 

@@ -1,0 +1,229 @@
+"""bench leg C3 (headline): cascaded 20+35 NMPC with obstacles on ippodromo, batch 65,536 per GPU.
+
+Workload: the controller config of the reference run race3_ippodromo (20 SingleTrack +
+35 PointMass stages, max_speed 18) with obstacles enabled (weight 10, the 7 ippodromo obstacles).  A closed-loop
+lap is first replayed on the engine itself from the reference's cold start (untimed); every tick gives a base
+state and the warm start the reference protocol would use there (previous solution, un-shifted).  Instance b
+takes tick b mod T, perturbs the initial state and jitters the obstacles (seed 1003 + rank).  The timed unit is
+one `command()`-equivalent: horizon parameters + one batched interior-point solve from that warm start.
+"""
+from __future__ import annotations
+
+import time
+
+import numpy as np
+
+import bench_common as bc
+
+SEED = 1003
+
+
+def controller_config(horizon_pm=35, obstacles=True, max_speed=18):
+    c = bc.load_yaml("controllers/cascaded.yaml")
+    c["horizon"], c["horizon_pm"], c["obstacles"] = 20, int(horizon_pm), bool(obstacles)
+    c["state_constraints"]["max_speed"] = max_speed
+    return c
+
+
+def replay_lap(eng, cfg, track, max_ticks=2000, obstacles=None):
+    """Closed loop of ONE vehicle on the engine (racing.py:217-242 semantics).  Returns per tick the state the
+    solve started from, the warm start it was given and the solution."""
+    import torch
+    from vehicle_control_b200.controllers.mpc.cascaded_mpc import cold_guess
+    N, H = int(cfg["horizon"]), int(cfg["horizon"]) + int(cfg["horizon_pm"])
+    X0, U0 = cold_guess(N, H, rng_draw=np.random.RandomState(31).random_sample((2, H)))
+    X, U = eng.tensor(X0[None]), eng.tensor(U0[None])
+    x = eng.tensor(np.array([[4.0, 0, 0, 0, 1.0, 0, 0, 0]]))
+    ob = None
+    if cfg.get("obstacles"):
+        oa = track.obstacle_array() if obstacles is None else obstacles
+        ob = eng.tensor(oa[None]) if len(oa) else None
+    rows = {"x0": [], "Xw": [], "Uw": [], "iters": [], "status": []}
+    for _ in range(max_ticks):
+        if float(x[0, 4]) > track.length - 0.1:
+            break
+        rows["x0"].append(x.cpu().numpy()[0]); rows["Xw"].append(X.cpu().numpy()[0]); rows["Uw"].append(U.cpu().numpy()[0])
+        ds, kap = eng.horizon_params(x, X)
+        out = eng.solve(x, kap, ds, X, U, obstacles=ob)
+        rows["iters"].append(int(out["iters"][0])); rows["status"].append(int(out["status"][0]))
+        if rows["status"][-1] > 1:
+            break
+        eng.plant_step(x, U[:, :, 0].contiguous())
+    return {k: np.array(v) for k, v in rows.items()}
+
+
+def make_batch(lap, track, B, seed, cfg):
+    """Perturbed initial states + per-instance obstacle jitter around the lap's ticks (SURVEY C2/C3 recipe)."""
+    rng = np.random.default_rng(seed)
+    ok = np.flatnonzero(lap["status"] <= 1)
+    ok = ok[ok >= 1]   # tick 0 has the cold guess, not a warm start
+    T = len(ok)
+    idx = ok[np.arange(B) % T]
+    x0 = lap["x0"][idx].copy()
+    x0[:, 0] = np.maximum(x0[:, 0] + rng.uniform(-.5, .5, B), 3.2)
+    x0[:, 1] += rng.normal(0, .05, B)
+    x0[:, 2] += rng.normal(0, .02, B)
+    x0[:, 3] = np.clip(x0[:, 3] + rng.uniform(-.02, .02, B), -.40, .40)
+    x0[:, 5] += rng.uniform(-.5, .5, B)
+    x0[:, 6] += rng.normal(0, .01, B)
+    x0[:, 7] = 0.0
+    obst = None
+    if cfg.get("obstacles"):
+        base = track.obstacle_array()
+        obst = np.repeat(base[None], B, 0)
+        obst[:, :, 0] += rng.uniform(-1, 1, (B, len(base)))
+        obst[:, :, 1] += rng.uniform(-.3, .3, (B, len(base)))
+        # keep the (perturbed) start outside every obstacle's radius + 1 m: fall back to the un-perturbed state
+        d = np.sqrt((x0[:, None, 4] - obst[:, :, 0]) ** 2 + (x0[:, None, 5] - obst[:, :, 1]) ** 2) - obst[:, :, 2]
+        bad = (d < 1.0).any(1)
+        x0[bad, 5] = lap["x0"][idx[bad], 5]
+        d = np.sqrt((x0[:, None, 4] - obst[:, :, 0]) ** 2 + (x0[:, None, 5] - obst[:, :, 1]) ** 2) - obst[:, :, 2]
+        bad = (d < 1.0).any(1)
+        obst[bad] = base   # still too close: drop the jitter as well
+    return x0, lap["Xw"][idx].copy(), lap["Uw"][idx].copy(), obst, idx
+
+
+# algorithmic flops of one interior-point iteration (SURVEY 8d convention: one flop per add/mul/div/sqrt/
+# compare-select/elementary function): N*(F_st_eval + F_ric) + M*(F_pm_eval + F_ric5)
+def flops_per_iteration(N, M):
+    return N * (15.0e3 + 4.0e3) + M * (0.5e3 + 1.5e3)
+
+
+def bytes_per_solve(H):
+    """compulsory traffic: read x0, kappa, ds, warm start; write solution + (obj, status, iters, kkt)."""
+    return 8.0 * ((8 + H + H + 10 * H) + (10 * H + 3))
+
+
+def cpu_baseline_nmpc(lap, track_yaml, cfg, seconds=25.0, procs=1):
+    """The CPU oracle (oracle/nlp.py + oracle/ipm.py: numpy/torch restatement of CasADi+IPOPT) solving warm-started
+    ticks of the same workload, `procs` single-threaded processes."""
+    import multiprocessing as mp
+    ticks = [int(t) for t in np.linspace(1, len(lap["x0"]) - 1, max(procs, 1) * 4).astype(int)]
+    args = [(track_yaml, cfg, lap["x0"][t], lap["Xw"][t], lap["Uw"][t]) for t in ticks]
+    t0 = time.perf_counter()
+    done = 0
+    if procs <= 1:
+        for a in args:
+            done += _oracle_solve(a)
+            if time.perf_counter() - t0 > seconds:
+                break
+    else:
+        with mp.get_context("spawn").Pool(procs) as pool:
+            for r in pool.imap_unordered(_oracle_solve, args[:procs * 2]):
+                done += r
+    el = time.perf_counter() - t0
+    return {"value": done / el, "unit": "solves/s", "cores": procs, "kind": "port",
+            "sample": f"{done} warm-started ticks of the same lap solved by the CPU oracle in {el:.1f} s "
+                      f"({procs} single-threaded process(es)); the reference's own logs report 14-25 solves/s "
+                      f"(IPOPT+MA27, 1 thread, BASELINE.md)"}
+
+
+def _oracle_solve(a):
+    import torch
+    torch.set_num_threads(1)
+    from oracle import ipm, models as om, nlp as on
+    from oracle.track import OracleTrack
+    track_yaml, cfg, x0, Xw, Uw = a
+    tr = OracleTrack(track_yaml)
+    c = on.MpcCfg.from_config(cfg)
+    ds, kap = on.horizon_params(c, tr, x0, Xw[0])
+    obst = np.array([o[:3] for o in tr.obstacles]) if c.obstacles else None
+    p = on.NLP(c, om.DEFAULT, x0, kap, ds, obst)
+    r = ipm.solve(p, p.pack(Xw, Uw))
+    return 1 if r.status in ("solved", "acceptable") else 0
+
+
+def run_nmpc(a, rank, world, local):
+    import torch
+    from vehicle_control_b200.engine import Engine
+    from vehicle_control_b200.environment.track import Track
+    B = a.batch or 65536
+    cfg = controller_config()
+    track_yaml = bc.load_yaml("environment/ippodromo.yaml")
+    tr = Track(track_yaml)
+    eng = Engine(bc.load_yaml("models/dynamic_car.yaml"), cfg, tr, device=local)
+    N, M = cfg["horizon"], cfg["horizon_pm"]
+    H = N + M
+    t0 = time.perf_counter()
+    lap = replay_lap(eng, cfg, tr)
+    lap_s = time.perf_counter() - t0
+    x0h, Xwh, Uwh, obh, _ = make_batch(lap, tr, B, SEED + rank, cfg)
+    x0, Xw, Uw, ob = eng.tensor(x0h), eng.tensor(Xwh), eng.tensor(Uwh), eng.tensor(obh)
+    X, U = torch.empty_like(Xw), torch.empty_like(Uw)
+    ds, kap = eng.empty(B, H), eng.empty(B, H)
+    out = {"obj": eng.empty(B), "status": eng.empty(B, dtype=torch.int32), "iters": eng.empty(B, dtype=torch.int32),
+           "kkt": eng.empty(B)}
+
+    def step():
+        X.copy_(Xw); U.copy_(Uw)                      # the warm start (solve is in place)
+        eng.horizon_params(x0, X, ds, kap)            # _init_horizon
+        eng.solve(x0, kap, ds, X, U, obstacles=ob, out=out)   # opti.solve()
+
+    eng.set_profiling(True)
+    l0 = eng.launch_count()
+    with bc.ClockSampler(local) as clk:
+        total_ms, per = bc.time_steps(step, a.steps, a.warmup)
+    launches_total = eng.launch_count() - l0
+    prof = eng.profile()
+    eng.set_profiling(False)
+    ms = total_ms / a.steps
+    value = world * B / (ms * 1e-3)
+    status, iters = out["status"].cpu().numpy(), out["iters"].cpu().numpy()
+    conv = float((status <= 1).mean())
+    mean_it = float(iters.mean())
+    runs = a.steps + a.warmup
+    # ---- e2e: host buffers through vc_nmpc_solve_host (H2D + solve + D2H inside the call)
+    Be = min(B, 16384) if a.e2e_batch == 0 else a.e2e_batch
+    hx0, hkap, hds = x0h[:Be].copy(), kap[:Be].cpu().numpy().copy(), ds[:Be].cpu().numpy().copy()
+    hob = obh[:Be].copy()
+    hX, hU = Xwh[:Be].copy(), Uwh[:Be].copy()
+    eng.solve_host(hx0, hkap, hds, hX, hU, obstacles=hob)   # warm-up (allocates the staging arena)
+    bc.barrier()
+    e2e_t = 0.0
+    for _ in range(max(1, min(a.steps, 3))):
+        hX[:], hU[:] = Xwh[:Be], Uwh[:Be]
+        t1 = time.perf_counter()
+        eng.solve_host(hx0, hkap, hds, hX, hU, obstacles=hob)
+        e2e_t += time.perf_counter() - t1
+    e2e_n = max(1, min(a.steps, 3))
+    e2e_s = bc.max_over_ranks(e2e_t / e2e_n)
+    h2d = (hx0.nbytes + hkap.nbytes + hds.nbytes + hob.nbytes + hX.nbytes + hU.nbytes)
+    d2h = hX.nbytes + hU.nbytes + Be * (8 + 8 + 4 + 4)
+    # ---- roofline of the dominant kernel (k_eval_st): algorithmic work / measured launch time
+    peak_hbm, how = bc.measured_peaks()
+    n_st = max(1, prof["launches"][0])
+    st_ms = prof["ms"][0] / n_st                       # average k_eval_st launch
+    step_ms = prof["ms"][2] / max(1, prof["launches"][2])
+    share = [m / max(1e-9, sum(prof["ms"])) for m in prof["ms"]]
+    # k_eval_st per launch: reads y, lam, z, s (38 doubles) and writes Hessian/Jacobian blocks (36+64+80+...=~230) per stage
+    st_bytes = B * N * 8.0 * (38 + 36 + 64 + 80 + 40 + 8 + 10 + 1)
+    st_flops = B * N * 15.0e3
+    fp64_peak = bc.FP64_PEAK_TFLOPS
+    solve_flops = mean_it * flops_per_iteration(N, M)
+    line = {
+        "metric": "NMPC solves/sec", "value": value, "unit": "solves/s", "n_gpus": world, "steps": a.steps,
+        "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "C3: cascaded NMPC 20+35 with obstacles, ippodromo, warm-started perturbed instances",
+                   "batch_per_gpu": B, "N": N, "M": M, "n_obstacles": int(obh.shape[1]), "tol": 1e-8,
+                   "converged_frac": conv, "mean_iters": mean_it, "max_iters": int(iters.max()),
+                   "lap_ticks": int(len(lap["x0"])), "lap_replay_s": lap_s,
+                   "l2": "per-step working set %.1f GB (solver workspace) >> 126 MB L2" % (eng.workspace_bytes() / 1e9)},
+        "clocks": clk.summary(), "gpu_launches": int(round(launches_total * a.steps / runs)),
+        "e2e": {"value": world * Be / e2e_s, "unit": "solves/s", "h2d_bytes_per_step": int(h2d),
+                "d2h_bytes_per_step": int(d2h), "batch": Be},
+        "roofline": {"bound": "hbm", "kernel": "k_eval_st", "achieved": st_bytes / (st_ms * 1e-3) / 1e9,
+                     "peak": peak_hbm, "unit": "GB/s", "frac": st_bytes / (st_ms * 1e-3) / 1e9 / peak_hbm,
+                     "traffic": None, "peak_source": how, "launch_ms": st_ms, "share_of_step": share[0],
+                     "fp64": {"achieved_tflops": st_flops / (st_ms * 1e-3) / 1e12, "peak_tflops": fp64_peak,
+                              "frac": st_flops / (st_ms * 1e-3) / 1e12 / fp64_peak,
+                              "peak_source": "measured DFMA micro-benchmark (profiles/r01_fp64_peak.txt)"},
+                     "whole_solve_fp64": {"achieved_tflops": value / world * solve_flops / 1e12,
+                                          "frac": value / world * solve_flops / 1e12 / fp64_peak,
+                                          "flops_per_solve": solve_flops},
+                     "kernel_share": {"k_eval_st": share[0], "k_eval_pm": share[1], "k_step": share[2]},
+                     "k_step_launch_ms": step_ms},
+    }
+    if rank == 0 and not a.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline_nmpc(lap, track_yaml, cfg)
+    return line

@@ -125,6 +125,20 @@ int vc_nmpc_solve_host(vc_handle* h, int B, const double* h_x0, const double* h_
                        const double* h_obst, int n_obs, double* h_X, double* h_U, double* h_obj,
                        int* h_status, int* h_iters, double* h_kkt);
 
+/* Measurement hooks (no reference counterpart; the reference times command() with time.time(), racing.py:231-233):
+ * with profiling on, vc_nmpc_solve brackets every kernel of its iteration loop with CUDA events on the handle's
+ * stream.  vc_get_profile: accumulated ms and launch counts of k_eval_st, k_eval_pm, k_step since
+ * vc_set_profiling, and the number of interior-point passes of the last solve. */
+int vc_set_profiling(vc_handle* h, int on);
+int vc_get_profile(vc_handle* h, double* out_ms3, long long* out_launches3, int* out_last_passes);
+
+/* Diagnostics: copies n doubles of solver-workspace array `array` (enum WsArray in csrc/vc_solver.cu; -1 = scalar
+ * block) of instance b of the last vc_nmpc_solve to the host.  Synchronises. */
+int vc_nmpc_debug_read(vc_handle* h, int b, int array, double* h_out, int n);
+
+/* bytes of device workspace currently held by the handle for vc_nmpc_solve */
+long long vc_workspace_bytes(vc_handle* h);
+
 /* number of kernels this handle has launched so far (bench bookkeeping) */
 long long vc_launch_count(vc_handle* h);
 

@@ -90,6 +90,9 @@ def solve(nlp, w0, opt: IpmOptions = IpmOptions()) -> IpmResult:
     objective scaling of the ORIGINAL initial point (that scaling decides where IPOPT's answer sits)."""
     res = _solve_once(nlp, w0, opt)
     restarts = 0
+    while res.status == "eval_error" and res.iters == 0 and restarts < opt.max_restorations and hasattr(nlp, "repair"):
+        restarts += 1          # invalid starting point: re-initialise, the repaired point sets the objective scaling
+        res = _solve_once(nlp, nlp.repair(res.w), opt)
     while res.status == "linesearch_fail" and restarts < opt.max_restorations and hasattr(nlp, "repair"):
         restarts += 1
         o2 = IpmOptions(**{**opt.__dict__, "obj_scale": res.obj_scale})

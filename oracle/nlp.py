@@ -139,7 +139,10 @@ class NLP:
             return 0.0
         so, eo, ro = self.obst[:, 0:1], self.obst[:, 1:2], self.obst[:, 2:3]
         dist = torch.sqrt((s[None] - so) ** 2 + (ey[None] - eo) ** 2)
-        return (self.cfg.w_obstacles * ds[None] / (dist - (ro + 0.1))).sum()
+        gap = dist - (ro + 0.1)
+        # inside the pole the term is negative and unbounded: treated as an evaluation error (NaN -> backtrack)
+        gap = torch.where(gap > 0, gap, torch.full_like(gap, float("nan")))
+        return (self.cfg.w_obstacles * ds[None] / gap).sum()
 
     def f(self, w):
         c, p, N, M, H = self.cfg, self.p, self.N, self.M, self.H
@@ -227,28 +230,36 @@ class NLP:
 
 
     # ------------------------------------------------------------ restoration substitute
-    def repair(self, w_np, neutral=True):
-        """Dynamically feasible re-initialisation used where IPOPT would enter its restoration phase:
-        controls clipped to their bounds, states re-generated by rolling the models out from x0."""
-        c, p, N, M = self.cfg, self.p, self.N, self.M
+    def repair(self, w_np):
+        """Guess-independent, dynamically feasible re-initialisation used where IPOPT would enter its
+        restoration phase: hold the current speed (Fx = drag), no steering rate, PointMass lateral force
+        that follows the centre-line curvature; states re-generated by rolling the models out from x0."""
+        p, N, M = self.p, self.N, self.M
         X, U = self.unpack(w_np)
         X, U = X.copy(), U.copy()
         kap, ds = self.kappa.numpy(), self.ds.numpy()
-        if neutral:   # guess-independent: coast straight ahead, PointMass holds the centre line
-            U[0, :] = 0.0
-            U[1, :] = 0.0
-        else:
-            U[1, :N] = np.clip(U[1, :N], c.w_min, c.w_max)
         X[:, 0] = self.x0.numpy()
-        for n in range(N - 1):
-            X[:, n + 1] = om.st_step_spatial(np, p, X[:, n][None], U[:, n][None], kap[n], ds[n])[0]
+        for n in range(N):
+            U[0, n] = p.Frr + p.Cd * X[0, n] ** 2
+            U[1, n] = 0.0
+            if n < N - 1:
+                X[:, n + 1] = om.st_step_spatial(np, p, X[:, n][None], U[:, n][None], kap[n], ds[n])[0]
         if M > 0:
             xl = X[:, N - 1]
             X[:5, N] = [np.hypot(xl[0], xl[1]), xl[4], xl[5], np.arctan(xl[1] / xl[0]) + xl[6], xl[7]]
-            for m in range(N, N + M - 1):
-                if neutral:
-                    U[1, m] = p.m * X[0, m] ** 2 * kap[m]
-                X[:5, m + 1] = om.pm_step_spatial(np, p, X[:5, m][None], U[:, m][None], kap[m], ds[m])[0]
+            for m in range(N, N + M):
+                U[0, m] = p.Frr + p.Cd * X[0, m] ** 2
+                U[1, m] = p.m * X[0, m] ** 2 * kap[m]
+                if m < N + M - 1:
+                    X[:5, m + 1] = om.pm_step_spatial(np, p, X[:5, m][None], U[:, m][None], kap[m], ds[m])[0]
+        # positions guessed inside an obstacle (pole of the reciprocal term; plus a margin) are moved sideways out
+        if self.obst is not None:
+            for k in range(1, N + M):
+                si, ei = (4, 5) if k < N else (1, 2)
+                for so, eo, ro in self.obst.numpy():
+                    R, a, e = ro + 0.1 + 0.5, X[si, k] - so, X[ei, k] - eo
+                    if a * a + e * e < R * R:
+                        X[ei, k] = eo + (1.0 if e > 0.0 else -1.0) * np.sqrt(R * R - a * a)
         return self.pack(X, U)
 
     # ------------------------------------------------------------ derivatives (exact, autodiff)

@@ -1,0 +1,112 @@
+"""NMPC controllers on the B200 engine.
+
+``CascadedMPC`` keeps the surface of the reference class (vehicle_control/controllers/mpc/cascaded_mpc.py:16-381:
+constructor (car, point_mass, config), ``command(state) -> DynamicCarAction``, ``state_prediction (8,H)``,
+``action_prediction (2,H)``, ``get_state_prediction() -> (H,3)``); ``horizon_pm: 0`` gives the plain
+singletrack controller (config/controllers/singletrack.yaml).  ``BatchedCascadedMPC`` is the same controller
+for B independent vehicles / problem instances with everything resident on the device.
+
+Per tick (reference :306-338): parameters ds, kappa from the previous prediction (k_horizon_params), warm start
+= previous solution un-shifted, then one batched interior-point solve (vc_nmpc_solve).  No CasADi, no IPOPT.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from ...engine import STATUS_NAMES, Engine
+from ...models.dynamic_car import DynamicCarAction
+from ...utils.common_utils import as_config
+from ..controller import Controller
+
+np.random.seed(31)   # cascaded_mpc.py:13 -- the cold guess of the actions is 1 + U[0,1) drawn at construction
+
+
+def cold_guess(N, H, rng_draw=None):
+    """_init_variables :72-76."""
+    X = np.ones((8, H))
+    X[0, :N] += 3
+    U = np.ones((2, H)) + (np.random.random((2, H)) if rng_draw is None else rng_draw)
+    return X, U
+
+
+class BatchedCascadedMPC(Controller):
+    def __init__(self, car, point_mass, config, batch: int, engine: Engine = None, obstacles=None):
+        self.config = as_config(config)
+        self.car, self.point_mass = car, point_mass
+        self.N, self.M = int(self.config.horizon), int(self.config.horizon_pm)
+        self.H = self.N + self.M
+        self.B = int(batch)
+        self.engine = engine if engine is not None else Engine(car.config, self.config, car.track)
+        if engine is not None:
+            self.engine.set_config(self.config)
+        e = self.engine
+        X, U = cold_guess(self.N, self.H)
+        self.state_prediction = e.tensor(np.repeat(X[None], self.B, 0))      # [B,8,H]
+        self.action_prediction = e.tensor(np.repeat(U[None], self.B, 0))     # [B,2,H]
+        self.ds, self.kappa = e.empty(self.B, self.H), e.empty(self.B, self.H)
+        self.info = {"obj": e.empty(self.B), "status": e.empty(self.B, dtype=torch.int32),
+                     "iters": e.empty(self.B, dtype=torch.int32), "kkt": e.empty(self.B)}
+        self.obstacles = None
+        if self.config.get("obstacles"):
+            ob = car.track.obstacle_array() if obstacles is None else np.asarray(obstacles, dtype=float)
+            if ob.ndim == 2:
+                ob = np.repeat(ob[None], self.B, 0)
+            self.obstacles = e.tensor(ob) if ob.shape[1] else None
+
+    def command(self, states: torch.Tensor) -> torch.Tensor:
+        """states [B,8] (device) -> first actions [B,2] (device view of action_prediction[:, :, 0])."""
+        e = self.engine
+        e.horizon_params(states, self.state_prediction, self.ds, self.kappa)
+        e.solve(states, self.kappa, self.ds, self.state_prediction, self.action_prediction,
+                obstacles=self.obstacles, out=self.info)
+        return self.action_prediction[:, :, 0].contiguous()
+
+    def get_state_prediction(self) -> torch.Tensor:
+        """[B,H,3] global (x, y, psi) of every predicted state (:340-352)."""
+        X, N = self.state_prediction, self.N
+        s = torch.cat([X[:, 4, :N], X[:, 1, N:]], 1).contiguous()
+        ey = torch.cat([X[:, 5, :N], X[:, 2, N:]], 1).contiguous()
+        ep = torch.cat([X[:, 6, :N], X[:, 3, N:]], 1).contiguous()
+        return self.engine.rel2glob(s, ey, ep)
+
+
+class CascadedMPC(Controller):
+    """Single-vehicle drop-in (B = 1) with the reference's attribute surface."""
+
+    def __init__(self, car, point_mass, config, engine: Engine = None):
+        self._batched = BatchedCascadedMPC(car, point_mass, config, 1, engine=engine)
+        self.config = self._batched.config
+        self.car, self.point_mass = car, point_mass
+        self.N, self.M, self.H = self._batched.N, self._batched.M, self._batched.H
+        self.ns, self.na, self.ns_pm, self.na_pm = 8, 2, 5, 2
+        self.dt = self.config.mpc_dt
+        self.last_info = None
+
+    @property
+    def state_prediction(self) -> np.ndarray:
+        return self._batched.state_prediction[0].cpu().numpy()
+
+    @state_prediction.setter
+    def state_prediction(self, v):
+        self._batched.state_prediction.copy_(self._batched.engine.tensor(np.asarray(v, dtype=float)[None]))
+
+    @property
+    def action_prediction(self) -> np.ndarray:
+        return self._batched.action_prediction[0].cpu().numpy()
+
+    @action_prediction.setter
+    def action_prediction(self, v):
+        self._batched.action_prediction.copy_(self._batched.engine.tensor(np.asarray(v, dtype=float)[None]))
+
+    def command(self, state):
+        x = np.asarray(getattr(state, "values", state), dtype=float).reshape(1, 8)
+        u = self._batched.command(self._batched.engine.tensor(x)).cpu().numpy()[0]
+        info = {k: v.cpu().numpy()[0] for k, v in self._batched.info.items()}
+        self.last_info = info
+        if int(info["status"]) > 1:   # the reference raises (CasADi RuntimeError) when IPOPT fails
+            raise RuntimeError(f"NMPC solve failed: {STATUS_NAMES.get(int(info['status']), info['status'])}")
+        return DynamicCarAction(Fx=float(u[0]), w=float(u[1]))
+
+    def get_state_prediction(self) -> np.ndarray:
+        return self._batched.get_state_prediction()[0].cpu().numpy()

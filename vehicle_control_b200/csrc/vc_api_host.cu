@@ -64,4 +64,29 @@ int vc_nmpc_solve_host(vc_handle* h, int B, const double* h_x0, const double* h_
     return check_cuda(cudaStreamSynchronize(st), "vc_nmpc_solve_host");
 }
 
+int vc_nmpc_debug_read(vc_handle* h, int b, int array, double* h_out, int n) {
+    if (!h || !h_out) { set_error("vc_nmpc_debug_read: null argument"); return -1; }
+    return debug_read(h, b, array, h_out, n);
+}
+
+long long vc_workspace_bytes(vc_handle* h) { return h ? (long long)h->ws_bytes : 0; }
+
+int vc_set_profiling(vc_handle* h, int on) {
+    if (!h) { set_error("vc_set_profiling: null handle"); return -1; }
+    h->profiling = on;
+    for (int i = 0; i < 4; ++i) h->prof_ms[i] = 0.0;
+    for (int i = 0; i < 3; ++i) h->prof_launches[i] = 0;
+    return 0;
+}
+
+int vc_get_profile(vc_handle* h, double* out_ms3, long long* out_launches3, int* out_last_passes) {
+    if (!h) { set_error("vc_get_profile: null handle"); return -1; }
+    for (int i = 0; i < 3; ++i) {
+        if (out_ms3) out_ms3[i] = h->prof_ms[i];
+        if (out_launches3) out_launches3[i] = h->prof_launches[i];
+    }
+    if (out_last_passes) *out_last_passes = h->last_passes;
+    return 0;
+}
+
 }  // extern "C"

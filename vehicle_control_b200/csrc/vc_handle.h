@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <string>
+#include <vector>
 #include "../../include/vc_api.h"
 
 struct vc_handle {
@@ -29,6 +30,11 @@ struct vc_handle {
     int* d_active = nullptr;
     int* h_active = nullptr;
     int last_passes = 0;
+    // optional per-kernel timing of the solver loop (vc_set_profiling)
+    int profiling = 0;
+    std::vector<cudaEvent_t> prof_events;
+    double prof_ms[4] = {0, 0, 0, 0};   // k_eval_st, k_eval_pm, k_step, launches of each
+    long long prof_launches[3] = {0, 0, 0};
 };
 
 namespace vc {
@@ -40,4 +46,5 @@ int launch_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_k
                       int* d_iters, double* d_kkt);
 int launch_nmpc_eval(vc_handle* h, int B, const double* d_x0, const double* d_kappa, const double* d_ds,
                      const double* d_obst, int n_obs, const double* d_X, const double* d_U, double* d_out);
+int debug_read(vc_handle* h, int b, int array, double* h_out, int n);
 }  // namespace vc

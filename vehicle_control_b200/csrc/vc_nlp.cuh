@@ -100,7 +100,9 @@ VC_HD void pm_cost_ineq(const Params& p, const Cfg& c, const T* y, double ds, bo
 }
 
 // ---- obstacle term of one stage (closed form): W ds / (dist - (radius + 0.1)), summed over obstacles.
-// Returns the value; g = d/d(s,ey); h = (ss, s-ey, ey-ey) second derivatives.
+// Returns the value; g = d/d(s,ey); h = (ss, s-ey, ey-ey) second derivatives.  Points inside an obstacle's pole
+// (dist <= radius + 0.1), where the reference's term turns negative and unbounded, evaluate to NaN so that the line
+// search treats them like IPOPT treats an evaluation error (backtrack); solutions outside are unaffected.
 VC_HD double obstacle_cost(const double* obst, int n_obs, double W, double ds, double s, double ey, double* g,
                            double* h) {
     double v = 0.0;
@@ -109,6 +111,7 @@ VC_HD double obstacle_cost(const double* obst, int n_obs, double W, double ds, d
     for (int o = 0; o < n_obs; ++o) {
         const double a = s - obst[3 * o], b = ey - obst[3 * o + 1], rad = obst[3 * o + 2] + 0.1;
         const double d = sqrt(a * a + b * b);
+        if (!(d > rad)) return NAN;   // inside the pole the reciprocal term is negative and unbounded: not a valid point
         const double q = 1.0 / (d - rad);
         const double k = W * ds;
         v += k * q;

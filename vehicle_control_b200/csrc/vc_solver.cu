@@ -46,13 +46,23 @@ enum WsArray {
     W_PM,        // [H][100] Riccati cost-to-go Hessians
     W_PV,        // [H][10]
     W_KM,        // [H][24]  feedback gains K[2][10], kff[2]
+    W_GT,        // [H][8]   equality residual at the last trial point
+    W_CT,        // [H][10]  inequality values at the last trial point
+    W_GS,        // [H][8]   second-order-correction residuals (equalities)
+    W_CS,        // [H][10]  second-order-correction residuals (c - s rows)
+    W_DY2,       // [H][10]  corrected direction
+    W_DLAM2,     // [H][8]
+    W_DSL2,      // [H][10]
+    W_DZ2,       // [H][10]
     W_COUNT
 };
 __host__ __device__ constexpr int ws_width(int a) {
     return a == W_Y ? 10 : a == W_LAM ? 8 : a == W_S ? 10 : a == W_Z ? 10 : a == W_HC ? 36 : a == W_AB ? 80
          : a == W_JC ? 80 : a == W_RD ? 10 : a == W_GF ? 10 : a == W_V1 ? 10 : a == W_V2 ? 10 : a == W_GRES ? 8
          : a == W_CRES ? 10 : a == W_FST ? 1 : a == W_OBS ? 6 : a == W_DY ? 10 : a == W_DLAM ? 8 : a == W_DSL ? 10
-         : a == W_DZ ? 10 : a == W_PM ? 100 : a == W_PV ? 10 : a == W_KM ? 24 : 0;
+         : a == W_DZ ? 10 : a == W_PM ? 100 : a == W_PV ? 10 : a == W_KM ? 24
+         : a == W_GT ? 8 : a == W_CT ? 10 : a == W_GS ? 8 : a == W_CS ? 10 : a == W_DY2 ? 10 : a == W_DLAM2 ? 8
+         : a == W_DSL2 ? 10 : a == W_DZ2 ? 10 : 0;
 }
 __host__ __device__ constexpr int ws_offset(int a) {   // offset in doubles PER STAGE before array a
     int o = 0;
@@ -63,7 +73,7 @@ constexpr int WS_PER_STAGE = ws_offset(W_COUNT);
 constexpr int NSCAL = 64;
 // scalar block of an instance
 enum Scal { S_MU = 0, S_SF, S_DELTA_LAST, S_THETA0, S_NFILT, S_ACC, S_MODE, S_RESTARTS, S_OBJ, S_ERR, S_ITERS,
-            S_STATUS, S_FILT = 16 /* theta[16] */, S_FILP = 32 /* phi[16] */ };
+            S_STATUS, S_DBG_ALPHA, S_DBG_AP, S_DBG_THETA, S_DBG_DPHI, S_FILT = 16, S_DBG_NAN = 50, S_DBG_THT0, S_DBG_PHT0, S_DBG_PHI, S_DBG_SOC, S_DBG_THT2, S_DBG_AP2 /* theta[16] */, S_FILP = 32 /* phi[16] */ };
 constexpr int FILT_MAX = 16;
 enum Mode { MODE_INIT = 0, MODE_STEP = 1, MODE_DONE = 2, MODE_REINIT = 3 };
 
@@ -80,6 +90,7 @@ struct Prob {   // device-side view of one vc_nmpc_solve call
     Params p;
     Cfg c;
     int B, N, M, H, n_obs;
+    double z_init;   // > 0: constant initial inequality multipliers (IPOPT warm_start_mult_bound_push); else mu/s
     const double *x0, *kappa, *ds, *obst;
     double *X, *U, *obj, *kkt;
     int *status, *iters;
@@ -335,7 +346,8 @@ __device__ __forceinline__ double slew_prev(const Prob& pr, const Ws& ws, int b,
 // Values of one stage at a trial point (plain doubles): objective share, constraint violation share,
 // log-barrier share.  y = stage variables, yn = next stage's (nullptr at the last stage), sl = trial slacks.
 struct StageVal { double f, theta, lns, gmax, cmin; };
-__device__ StageVal stage_trial(const Prob& pr, int b, int k, const double* y, const double* yn, const double* sl) {
+__device__ StageVal stage_trial(const Prob& pr, int b, int k, const double* y, const double* yn, const double* sl,
+                                double* og0 = nullptr, double* ogn = nullptr, double* oc = nullptr) {
     StageVal o{0.0, 0.0, 0.0, 0.0, INFINITY};
     const int H = pr.H, N = pr.N;
     const double kap = pr.kappa[(size_t)b * H + k];
@@ -348,20 +360,20 @@ __device__ StageVal stage_trial(const Prob& pr, int b, int k, const double* y, c
         st_cost_ineq(pr.p, pr.c, y, ds, k == N - 1 && pr.M == 0, cost, ineq);
         o.f = cost;
 #pragma unroll
-        for (int j = 0; j < NI_ST; ++j) { o.theta += fabs(ineq[j] - sl[j]); o.lns += log(sl[j]); o.cmin = fmin(o.cmin, ineq[j]); }
+        for (int j = 0; j < NI_ST; ++j) { o.theta += fabs(ineq[j] - sl[j]); o.lns += log(sl[j]); o.cmin = fmin(o.cmin, ineq[j]); if (oc) oc[j] = ineq[j]; }
         if (k == 0)
-            for (int i = 0; i < 8; ++i) { const double e = fabs(y[i] - pr.x0[(size_t)b * 8 + i]); o.theta += e; o.gmax = nmax(o.gmax, e); }
+            for (int i = 0; i < 8; ++i) { const double r = y[i] - pr.x0[(size_t)b * 8 + i], e = fabs(r); o.theta += e; o.gmax = nmax(o.gmax, e); if (og0) og0[i] = r; }
         if (k < N - 1) {
             double xn[8];
             st_rk4<true>(pr.p, y, y + 8, kap, ds, xn);
 #pragma unroll
-            for (int i = 0; i < 8; ++i) { const double e = fabs(yn[i] - xn[i]); o.theta += e; o.gmax = nmax(o.gmax, e); }
+            for (int i = 0; i < 8; ++i) { const double r = yn[i] - xn[i], e = fabs(r); o.theta += e; o.gmax = nmax(o.gmax, e); if (ogn) ogn[i] = r; }
             o.f += c0 * sq(yn[8] - y[8]);
         } else if (pr.M > 0) {
             double xp[5], T;
             st_switch(pr.p, y, xp, T);
 #pragma unroll
-            for (int i = 0; i < 5; ++i) { const double e = fabs(yn[i] - xp[i]); o.theta += e; o.gmax = nmax(o.gmax, e); }
+            for (int i = 0; i < 5; ++i) { const double r = yn[i] - xp[i], e = fabs(r); o.theta += e; o.gmax = nmax(o.gmax, e); if (ogn) ogn[i] = r; }
             o.f += c0 * (sq(yn[QFX] - y[8]) + sq(yn[QFY] - T));
         }
         if (pr.c.obstacles && pr.n_obs > 0)
@@ -372,12 +384,12 @@ __device__ StageVal stage_trial(const Prob& pr, int b, int k, const double* y, c
         double cost, ineq[NI_PM];
         pm_cost_ineq(pr.p, pr.c, y, ds, k == H - 1, cost, ineq);
         o.f = cost;
-        for (int j = 0; j < NI_PM; ++j) { o.theta += fabs(ineq[j] - sl[j]); o.lns += log(sl[j]); o.cmin = fmin(o.cmin, ineq[j]); }
+        for (int j = 0; j < NI_PM; ++j) { o.theta += fabs(ineq[j] - sl[j]); o.lns += log(sl[j]); o.cmin = fmin(o.cmin, ineq[j]); if (oc) oc[j] = ineq[j]; }
         if (k < H - 1) {
             double xn[5];
             pm_euler<true>(pr.p, y, y + 5, kap, ds, xn);
 #pragma unroll
-            for (int i = 0; i < 5; ++i) { const double e = fabs(yn[i] - xn[i]); o.theta += e; o.gmax = nmax(o.gmax, e); }
+            for (int i = 0; i < 5; ++i) { const double r = yn[i] - xn[i], e = fabs(r); o.theta += e; o.gmax = nmax(o.gmax, e); if (ogn) ogn[i] = r; }
             o.f += c0 * sq(yn[QFX] - y[QFX]) + c1 * sq(yn[QFY] - y[QFY]);
         }
         if (pr.c.obstacles && pr.n_obs > 0)
@@ -494,7 +506,7 @@ __device__ void init_slacks(const Prob& pr, const Ws& ws, int b, int lane, doubl
         double *s = ws.at(b, W_S, k), *z = ws.at(b, W_Z, k), *lam = ws.at(b, W_LAM, k);
         for (int j = 0; j < (k < pr.N ? NI_ST : NI_PM); ++j) {
             s[j] = fmax(cr[j], IpmConst::slack_push * fmax(1.0, fabs(cr[j])));
-            z[j] = mu / s[j];
+            z[j] = pr.z_init > 0.0 ? pr.z_init : mu / s[j];
         }
         for (int i = 0; i < 8; ++i) lam[i] = 0.0;
     }
@@ -530,7 +542,7 @@ __device__ __forceinline__ int gpos(const Dims& d, int i) { return i < d.nu_off 
 
 // builds M = [A~ B~] (rows: lifted next state, cols: [x | p | u] of stage k) and r~ in shared memory
 __device__ void build_transition(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int lane, int k, const Dims& d,
-                                 const Dims& dn) {
+                                 const Dims& dn, int a_gres) {
     const int nn = d.n + 2;
     for (int e = lane; e < dn.n * 12; e += 32) sm.M[e] = 0.0;
     __syncwarp();
@@ -549,7 +561,7 @@ __device__ void build_transition(const Prob& pr, const Ws& ws, WarpSm& sm, int b
     }
     if (dn.np > 1 && d.st && lane < 8)                             // p1 <- T(y_{N-1}) = Fy_f + Fy_r
         sm.M[(dn.nx + 1) * 12 + gpos(d, c_act_st[lane])] = ab[5 * 8 + lane];
-    if (lane < dn.n) sm.r[lane] = lane < dn.nx ? -ws.at(b, W_GRES, k + 1)[lane] : 0.0;
+    if (lane < dn.n) sm.r[lane] = lane < dn.nx ? -ws.at(b, a_gres, k + 1)[lane] : 0.0;
     (void)nn;
     __syncwarp();
 }
@@ -558,8 +570,10 @@ __device__ void build_transition(const Prob& pr, const Ws& ws, WarpSm& sm, int b
 //   [Hc + delta I  Jg^T] [dw  ]   [-(rd - mu v1 + v2)]
 //   [Jg            0   ] [dlam] = [-g                ]
 // Returns false when some reduced Hessian block is not positive definite (wrong inertia for this delta).
-__device__ bool riccati(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int lane, double mu, double delta) {
+__device__ bool riccati(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int lane, double mu, double delta, bool soc) {
     const int H = pr.H, N = pr.N;
+    // second-order correction: same matrix, residuals replaced by the accumulated c_soc (IPOPT 2.4 / Alg. A-5.7)
+    const int a_gres = soc ? W_GS : W_GRES, a_dy = soc ? W_DY2 : W_DY, a_dlam = soc ? W_DLAM2 : W_DLAM;
     const double sf = ws.scal(b)[S_SF];
     const double* dsb = pr.ds + (size_t)b * H;
     bool ok = true;
@@ -580,7 +594,20 @@ __device__ bool riccati(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int lan
                 sm.G[pb * 12 + pa] = v;
             }
             const double *rd = ws.at(b, W_RD, k), *v1 = ws.at(b, W_V1, k), *v2 = ws.at(b, W_V2, k);
-            if (lane < d.nx + 2) sm.g[gpos(d, lane)] = rd[lane] - mu * v1[lane] + v2[lane];
+            if (lane < d.nx + 2) {
+                double f = rd[lane] - mu * v1[lane] + v2[lane];
+                if (soc) {   // + Jc^T sigma (c_soc - (c - s))
+                    const int a = d.st ? (lane < 4 ? lane : lane == 5 ? 4 : lane == 6 ? 5 : lane >= 8 ? lane - 2 : -1)
+                                       : (lane == 0 ? 0 : lane == 2 ? 1 : lane == 3 ? 2 : lane >= 5 ? lane - 2 : -1);
+                    if (a >= 0) {
+                        const double *jc = ws.at(b, W_JC, k), *cs = ws.at(b, W_CS, k), *cr = ws.at(b, W_CRES, k);
+                        const double *s = ws.at(b, W_S, k), *z = ws.at(b, W_Z, k);
+                        for (int j = 0; j < (d.st ? NI_ST : NI_PM); ++j)
+                            f += jc[j * 8 + a] * (z[j] / s[j]) * (cs[j] - (cr[j] - s[j]));
+                    }
+                }
+                sm.g[gpos(d, lane)] = f;
+            }
             if (lane >= d.nx && lane < n) sm.g[lane] = 0.0;   // lifted variables carry no linear term
         }
         __syncwarp();
@@ -607,7 +634,7 @@ __device__ bool riccati(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int lan
         __syncwarp();
         if (k < H - 1) {
             const Dims dn = stage_dims(N, k + 1);
-            build_transition(pr, ws, sm, b, lane, k, d, dn);
+            build_transition(pr, ws, sm, b, lane, k, d, dn, a_gres);
             for (int e = lane; e < dn.n * nn; e += 32) {      // PMm = P M
                 const int i = e / nn, j = e % nn;
                 double a = 0.0;
@@ -672,7 +699,7 @@ __device__ bool riccati(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int lan
     }
     if (!ok) return false;
     // ---- forward substitution
-    if (lane < 12) sm.x[lane] = lane < 8 ? -ws.at(b, W_GRES, 0)[lane] : 0.0;
+    if (lane < 12) sm.x[lane] = lane < 8 ? -ws.at(b, a_gres, 0)[lane] : 0.0;
     __syncwarp();
     for (int k = 0; k < H; ++k) {
         const Dims d = stage_dims(N, k);
@@ -684,18 +711,18 @@ __device__ bool riccati(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int lan
             sm.x[n + lane] = a;
         }
         __syncwarp();
-        double* dy = ws.at(b, W_DY, k);
+        double* dy = ws.at(b, a_dy, k);
         if (lane < d.nx) {
             dy[lane] = sm.x[lane];
             const double* pm = ws.at(b, W_PM, k);
             double a = ws.at(b, W_PV, k)[lane];
             for (int l = 0; l < n; ++l) a += pm[lane * 10 + l] * sm.x[l];
-            ws.at(b, W_DLAM, k)[lane] = -a;
+            ws.at(b, a_dlam, k)[lane] = -a;
         }
         if (lane < 2) dy[d.nu_off + lane] = sm.x[n + lane];
         if (k < H - 1) {
             const Dims dn = stage_dims(N, k + 1);
-            build_transition(pr, ws, sm, b, lane, k, d, dn);
+            build_transition(pr, ws, sm, b, lane, k, d, dn, a_gres);
             double a = 0.0;
             if (lane < dn.n) {
                 a = sm.r[lane];
@@ -709,7 +736,77 @@ __device__ bool riccati(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int lan
     return true;
 }
 
-// restoration substitute (oracle/nlp.py NLP.repair): clip the steering rate, roll the models out from x0
+// slack / multiplier directions of a computed primal direction, fraction-to-the-boundary step sizes and the
+// directional derivative of the barrier objective (warp reductions)
+__device__ void slack_directions(const Prob& pr, const Ws& ws, int b, int lane, double mu, double tau, bool soc,
+                                 double& a_p, double& a_d, double& dphi) {
+    const int H = pr.H, N = pr.N;
+    a_p = 1.0; a_d = 1.0; dphi = 0.0;
+    for (int k = lane; k < H; k += 32) {
+        const bool st = k < N;
+        const int na = st ? 8 : 5;
+        const double *jc = ws.at(b, W_JC, k), *dy = ws.at(b, soc ? W_DY2 : W_DY, k), *cr = ws.at(b, W_CRES, k);
+        const double *s = ws.at(b, W_S, k), *z = ws.at(b, W_Z, k), *gf = ws.at(b, W_GF, k), *cs = ws.at(b, W_CS, k);
+        double *dsl = ws.at(b, soc ? W_DSL2 : W_DSL, k), *dz = ws.at(b, soc ? W_DZ2 : W_DZ, k);
+        for (int j = 0; j < (st ? NI_ST : NI_PM); ++j) {
+            double a = soc ? cs[j] : cr[j] - s[j];
+            for (int q = 0; q < na; ++q) a += jc[j * 8 + q] * dy[st ? c_act_st[q] : c_act_pm[q]];
+            const double dzj = mu / s[j] - z[j] - (z[j] / s[j]) * a;
+            dsl[j] = a; dz[j] = dzj;
+            if (a < 0.0) a_p = fmin(a_p, -tau * s[j] / a);
+            if (dzj < 0.0) a_d = fmin(a_d, -tau * z[j] / dzj);
+            dphi -= mu * a / s[j];
+        }
+        for (int i = 0; i < (st ? 10 : 7); ++i) dphi += gf[i] * dy[i];
+    }
+    a_p = warp_min(a_p); a_d = warp_min(a_d); dphi = warp_sum(dphi);
+}
+
+// evaluates the trial point (y + alpha dy, s + alpha ds) with lanes over stages; optionally keeps the constraint
+// values for a second-order correction.  Returns false on an evaluation error (NaN/Inf).
+__device__ bool trial_point(const Prob& pr, const Ws& ws, int b, int lane, double alpha, bool soc, bool store,
+                            double& ft, double& tht, double& lnt) {
+    const int H = pr.H, N = pr.N;
+    ft = 0.0; tht = 0.0; lnt = 0.0;
+    const int a_dy = soc ? W_DY2 : W_DY, a_ds = soc ? W_DSL2 : W_DSL;
+    for (int k = lane; k < H; k += 32) {
+        double yt[10], yn[10], st_[10];
+        const int nv = k < N ? 10 : 7;
+        const double *y = ws.at(b, W_Y, k), *dy = ws.at(b, a_dy, k);
+        for (int i = 0; i < nv; ++i) yt[i] = y[i] + alpha * dy[i];
+        if (k < H - 1) {
+            const double *y1 = ws.at(b, W_Y, k + 1), *dy1 = ws.at(b, a_dy, k + 1);
+            for (int i = 0; i < (k + 1 < N ? 10 : 7); ++i) yn[i] = y1[i] + alpha * dy1[i];
+        }
+        const double *s = ws.at(b, W_S, k), *dsl = ws.at(b, a_ds, k);
+        for (int j = 0; j < (k < N ? NI_ST : NI_PM); ++j) st_[j] = s[j] + alpha * dsl[j];
+        const StageVal v = stage_trial(pr, b, k, yt, yn, st_, store ? ws.at(b, W_GT, 0) : nullptr,
+                                       store && k < H - 1 ? ws.at(b, W_GT, k + 1) : nullptr, store ? ws.at(b, W_CT, k) : nullptr);
+        if (store)   // c(x_trial) - s_trial
+            for (int j = 0; j < (k < N ? NI_ST : NI_PM); ++j) ws.at(b, W_CT, k)[j] -= st_[j];
+        ft += v.f; tht += v.theta; lnt += v.lns;
+    }
+    ft = warp_sum(ft); tht = warp_sum(tht); lnt = warp_sum(lnt);
+    __syncwarp();
+    return isfinite(ft) && isfinite(tht) && isfinite(lnt);
+}
+
+// c_soc <- alpha * (first ? c(x_k) : c_soc) + c(trial)      for the equality rows and the (c - s) rows
+__device__ void soc_residual(const Prob& pr, const Ws& ws, int b, int lane, double alpha, bool /*soc*/, bool first) {
+    for (int k = lane; k < pr.H; k += 32) {
+        const bool st = k < pr.N;
+        double *gs = ws.at(b, W_GS, k), *cs = ws.at(b, W_CS, k);
+        const double *gt = ws.at(b, W_GT, k), *ct = ws.at(b, W_CT, k), *gr = ws.at(b, W_GRES, k);
+        const double *cr = ws.at(b, W_CRES, k), *s = ws.at(b, W_S, k);
+        for (int i = 0; i < (st ? 8 : 5); ++i) gs[i] = alpha * (first ? gr[i] : gs[i]) + gt[i];
+        for (int j = 0; j < (st ? NI_ST : NI_PM); ++j) cs[j] = alpha * (first ? cr[j] - s[j] : cs[j]) + ct[j];
+    }
+    __syncwarp();
+}
+
+// restoration substitute (oracle/nlp.py NLP.repair): guess-independent, dynamically feasible re-initialisation
+// -- hold the speed (Fx = drag), no steering rate, PointMass Fy follows the centre-line curvature -- with the
+// states re-generated by rolling the models out from x0
 __device__ void repair_rollout(const Prob& pr, const Ws& ws, int b) {
     const int H = pr.H, N = pr.N;
     const double* kap = pr.kappa + (size_t)b * H;
@@ -718,15 +815,31 @@ __device__ void repair_rollout(const Prob& pr, const Ws& ws, int b) {
     for (int i = 0; i < 8; ++i) y[i] = pr.x0[(size_t)b * 8 + i];
     for (int k = 0; k < N; ++k) {
         y = ws.at(b, W_Y, k);
-        y[YW] = fmin(fmax(y[YW], pr.c.w_min), pr.c.w_max);
+        y[YFX] = pr.p.Frr + pr.p.Cd * y[IUX] * y[IUX];
+        y[YW] = 0.0;
         if (k < N - 1) st_rk4<true>(pr.p, y, y + 8, kap[k], dsb[k], ws.at(b, W_Y, k + 1));
     }
     if (pr.M > 0) {
         double T;
         st_switch(pr.p, ws.at(b, W_Y, N - 1), ws.at(b, W_Y, N), T);
-        for (int k = N; k < H - 1; ++k) {
+        for (int k = N; k < H; ++k) {
             y = ws.at(b, W_Y, k);
-            pm_euler<true>(pr.p, y, y + 5, kap[k], dsb[k], ws.at(b, W_Y, k + 1));
+            y[QFX] = pr.p.Frr + pr.p.Cd * y[QV] * y[QV];
+            y[QFY] = pr.p.m * y[QV] * y[QV] * kap[k];
+            if (k < H - 1) pm_euler<true>(pr.p, y, y + 5, kap[k], dsb[k], ws.at(b, W_Y, k + 1));
+        }
+    }
+    // the obstacle term has a pole at dist = radius + 0.1 and is negative inside it: move guessed positions that
+    // fall inside an obstacle (plus a margin) sideways out of it (towards the side they are on; dead centre -> right)
+    if (pr.c.obstacles && pr.n_obs > 0) {
+        const double* ob = pr.obst + (size_t)b * pr.n_obs * 3;
+        for (int k = 1; k < H; ++k) {
+            y = ws.at(b, W_Y, k);
+            const int si = k < N ? IS : QS, eyi = k < N ? IEY : QEY;
+            for (int o = 0; o < pr.n_obs; ++o) {
+                const double R = ob[3 * o + 2] + 0.1 + 0.5, a = y[si] - ob[3 * o], e = y[eyi] - ob[3 * o + 1];
+                if (a * a + e * e < R * R) y[eyi] = ob[3 * o + 1] + (e > 0.0 ? 1.0 : -1.0) * sqrt(R * R - a * a);
+            }
         }
     }
 }
@@ -750,7 +863,14 @@ __global__ void __launch_bounds__(32 * STEP_WARPS) k_step(Prob pr, Ws ws, int* n
     double mu = sc[S_MU];
     const double sf = sc[S_SF];
     if (mode == MODE_INIT || mode == MODE_REINIT) {
-        if (!finite) { finalize(pr, ws, b, lane, VC_EVAL_ERROR, m.f, INFINITY); return; }
+        if (!finite) {   // invalid starting point (NaN / inside an obstacle pole): restoration substitute, else give up
+            const int restarts = (int)sc[S_RESTARTS];
+            if (restarts >= 2) { finalize(pr, ws, b, lane, VC_EVAL_ERROR, m.f, INFINITY); return; }
+            __syncwarp();
+            // (an invalid FIRST point has no gradient to scale by: the repaired point then sets the objective scaling)
+            if (lane == 0) { repair_rollout(pr, ws, b); sc[S_RESTARTS] = restarts + 1; sc[S_MODE] = mode; }
+            return;
+        }
         if (mode == MODE_INIT && c.obj_scaling && m.gfmax > IpmConst::max_gradient && lane == 0)
             sc[S_SF] = IpmConst::max_gradient / m.gfmax;   // gradient-based objective scaling at the initial point
         init_slacks(pr, ws, b, lane, mu);
@@ -784,79 +904,77 @@ __global__ void __launch_bounds__(32 * STEP_WARPS) k_step(Prob pr, Ws ws, int* n
     const double theta_min = 1e-4 * fmax(1.0, theta0), theta_max = 1e4 * fmax(1.0, theta0);
     const double delta_last = sc[S_DELTA_LAST];
     const bool first_ever = delta_last == 0.0;
-    double trial = 0.0, alpha = 0.0, a_d = 1.0;
+    double trial = 0.0, alpha = 0.0, a_d = 1.0, dbg_ap = 0.0, dbg_dphi = 0.0, dbg_tht0 = 0.0, dbg_pht0 = 0.0;
+    int dbg_nan = 0;
+    double dbg_tht2 = 0.0, dbg_ap2 = 0.0;
     bool accepted = false, failed = false;
     double* filt_t = sc + S_FILT;
     double* filt_p = sc + S_FILP;
+    bool use_soc = false;
+    // acceptance of a trial point by the filter (IPOPT Alg. A, steps A-5.3/5.4); all lanes hold the same values
+    auto acceptable = [&](double a_test, double tht, double pht, double dphi, bool& augment) -> bool {
+        augment = false;
+        if (tht > theta_max) return false;
+        for (int i = 0; i < nfilt; ++i)
+            if (tht >= filt_t[i] && pht >= filt_p[i]) return false;
+        const bool switching = theta <= theta_min && dphi < 0.0 &&
+                               a_test * pow(-dphi, IpmConst::s_phi) > IpmConst::delta * pow(theta, IpmConst::s_theta);
+        if (switching) {
+            if (pht <= phi + IpmConst::eta_phi * a_test * dphi) return true;
+        } else if (tht <= (1 - IpmConst::gamma_theta) * theta || pht <= phi - IpmConst::gamma_phi * theta) {
+            augment = true;
+            return true;
+        }
+        // steps at the rounding floor: both measures unchanged
+        return fabs(pht - phi) <= 1e-13 * fmax(1.0, fabs(phi)) && tht <= theta + 1e-13;
+    };
     while (!accepted && !failed) {
         // ---- inertia-correcting factorisation (IPOPT delta_w ladder)
-        while (!riccati(pr, ws, sm, b, lane, mu, trial)) {
+        while (!riccati(pr, ws, sm, b, lane, mu, trial, false)) {
             if (trial == 0.0) trial = first_ever ? 1e-4 : fmax(1e-20, delta_last / 3.0);
             else trial *= first_ever ? 100.0 : 8.0;
             if (trial > 1e40) { failed = true; break; }
         }
         if (failed) break;
-        // ---- slack / multiplier directions, fraction to the boundary, directional derivative
-        double a_p = 1.0, dphi = 0.0;
-        a_d = 1.0;
-        for (int k = lane; k < H; k += 32) {
-            const bool st = k < N;
-            const int na = st ? 8 : 5;
-            const double *jc = ws.at(b, W_JC, k), *dy = ws.at(b, W_DY, k), *cr = ws.at(b, W_CRES, k);
-            const double *s = ws.at(b, W_S, k), *z = ws.at(b, W_Z, k), *gf = ws.at(b, W_GF, k);
-            double *dsl = ws.at(b, W_DSL, k), *dz = ws.at(b, W_DZ, k);
-            for (int j = 0; j < (st ? NI_ST : NI_PM); ++j) {
-                double a = cr[j] - s[j];
-                for (int q = 0; q < na; ++q) a += jc[j * 8 + q] * dy[st ? c_act_st[q] : c_act_pm[q]];
-                const double dzj = mu / s[j] - z[j] - (z[j] / s[j]) * a;
-                dsl[j] = a; dz[j] = dzj;
-                if (a < 0.0) a_p = fmin(a_p, -tau * s[j] / a);
-                if (dzj < 0.0) a_d = fmin(a_d, -tau * z[j] / dzj);
-                dphi -= mu * a / s[j];
-            }
-            for (int i = 0; i < (st ? 10 : 7); ++i) dphi += gf[i] * dy[i];
-        }
-        a_p = warp_min(a_p); a_d = warp_min(a_d); dphi = warp_sum(dphi);
-        // ---- filter line search, lanes over stages
+        double a_p, dphi;
+        slack_directions(pr, ws, b, lane, mu, tau, false, a_p, a_d, dphi);
+        dbg_ap = a_p; dbg_dphi = dphi;
+        // ---- backtracking filter line search, lanes over stages
         alpha = a_p;
         for (int bt = 0; bt < 12 && !accepted; ++bt, alpha *= 0.5) {
-            double ft = 0.0, tht = 0.0, lnt = 0.0;
-            for (int k = lane; k < H; k += 32) {
-                double yt[10], yn[10], st_[10];
-                const int nv = k < N ? 10 : 7;
-                const double *y = ws.at(b, W_Y, k), *dy = ws.at(b, W_DY, k);
-                for (int i = 0; i < nv; ++i) yt[i] = y[i] + alpha * dy[i];
-                if (k < H - 1) {
-                    const double *y1 = ws.at(b, W_Y, k + 1), *dy1 = ws.at(b, W_DY, k + 1);
-                    for (int i = 0; i < (k + 1 < N ? 10 : 7); ++i) yn[i] = y1[i] + alpha * dy1[i];
-                }
-                const double *s = ws.at(b, W_S, k), *dsl = ws.at(b, W_DSL, k);
-                for (int j = 0; j < (k < N ? NI_ST : NI_PM); ++j) st_[j] = s[j] + alpha * dsl[j];
-                const StageVal v = stage_trial(pr, b, k, yt, yn, st_);
-                ft += v.f; tht += v.theta; lnt += v.lns;
-            }
-            ft = warp_sum(ft); tht = warp_sum(tht); lnt = warp_sum(lnt);
-            if (!(isfinite(ft) && isfinite(tht) && isfinite(lnt))) continue;   // evaluation error: backtrack
-            const double pht = sf * ft - mu * lnt;
-            bool in_filter = tht > theta_max;
-            for (int i = 0; i < nfilt; ++i) in_filter = in_filter || (tht >= filt_t[i] && pht >= filt_p[i]);
-            if (in_filter) continue;
-            const bool switching = theta <= theta_min && dphi < 0.0 &&
-                                   alpha * pow(-dphi, IpmConst::s_phi) > IpmConst::delta * pow(theta, IpmConst::s_theta);
+            double ft, tht, lnt;
+            const bool okv = trial_point(pr, ws, b, lane, alpha, false, bt == 0, ft, tht, lnt);
+            if (!okv) ++dbg_nan;
+            if (bt == 0) { dbg_tht0 = tht; dbg_pht0 = sf * ft - mu * lnt; }
             bool augment = false;
-            if (switching) {
-                if (pht <= phi + IpmConst::eta_phi * alpha * dphi) accepted = true;
-            } else if (tht <= (1 - IpmConst::gamma_theta) * theta || pht <= phi - IpmConst::gamma_phi * theta) {
-                accepted = true; augment = true;
+            if (okv && acceptable(alpha, tht, sf * ft - mu * lnt, dphi, augment)) accepted = true;
+            // ---- second-order correction (IPOPT Alg. A-5.5 .. A-5.9): first trial step rejected and infeasibility
+            // not reduced -> re-solve with c_soc = alpha c(x) + c(x + alpha d), at most 4 times
+            if (!accepted && bt == 0 && okv && tht >= theta) {
+                soc_residual(pr, ws, b, lane, alpha, false, true);
+                double theta_soc_old = theta;
+                for (int ps = 0; ps < 4; ++ps) {
+                    if (!riccati(pr, ws, sm, b, lane, mu, trial, true)) break;
+                    double a_p2, a_d2, dphi2, ft2, tht2, lnt2;
+                    slack_directions(pr, ws, b, lane, mu, tau, true, a_p2, a_d2, dphi2);
+                    const bool ok2 = trial_point(pr, ws, b, lane, a_p2, true, true, ft2, tht2, lnt2);
+                    if (ps == 0) { dbg_tht2 = ok2 ? tht2 : -1.0; dbg_ap2 = a_p2; }
+                    if (ok2 && acceptable(alpha, tht2, sf * ft2 - mu * lnt2, dphi, augment)) {
+                        accepted = true; use_soc = true; alpha = a_p2; a_d = a_d2;
+                        break;
+                    }
+                    if (!ok2 || tht2 > 0.99 * theta_soc_old) break;
+                    theta_soc_old = tht2;
+                    soc_residual(pr, ws, b, lane, a_p2, true, false);
+                }
             }
-            if (!accepted && fabs(pht - phi) <= 1e-13 * fmax(1.0, fabs(phi)) && tht <= theta + 1e-13) accepted = true;
-            if (accepted && augment) {
-                if (nfilt < FILT_MAX) {
+            if (accepted) {
+                if (augment && nfilt < FILT_MAX) {
                     if (lane == 0) { filt_t[nfilt] = (1 - IpmConst::gamma_theta) * theta; filt_p[nfilt] = phi - IpmConst::gamma_phi * theta; }
                     ++nfilt;
                 }
+                break;
             }
-            if (accepted) break;
         }
         __syncwarp();
         if (accepted) break;
@@ -884,7 +1002,8 @@ __global__ void __launch_bounds__(32 * STEP_WARPS) k_step(Prob pr, Ws ws, int* n
     for (int k = lane; k < H; k += 32) {
         const bool st = k < N;
         double *y = ws.at(b, W_Y, k), *lam = ws.at(b, W_LAM, k), *s = ws.at(b, W_S, k), *z = ws.at(b, W_Z, k);
-        const double *dy = ws.at(b, W_DY, k), *dl = ws.at(b, W_DLAM, k), *dsl = ws.at(b, W_DSL, k), *dz = ws.at(b, W_DZ, k);
+        const double *dy = ws.at(b, use_soc ? W_DY2 : W_DY, k), *dl = ws.at(b, use_soc ? W_DLAM2 : W_DLAM, k);
+        const double *dsl = ws.at(b, use_soc ? W_DSL2 : W_DSL, k), *dz = ws.at(b, use_soc ? W_DZ2 : W_DZ, k);
         for (int i = 0; i < (st ? 10 : 7); ++i) y[i] += alpha * dy[i];
         for (int i = 0; i < (st ? 8 : 5); ++i) lam[i] += alpha * dl[i];
         for (int j = 0; j < (st ? NI_ST : NI_PM); ++j) {
@@ -898,6 +1017,9 @@ __global__ void __launch_bounds__(32 * STEP_WARPS) k_step(Prob pr, Ws ws, int* n
         sc[S_MU] = mu; sc[S_NFILT] = nfilt; sc[S_THETA0] = theta0; sc[S_ACC] = acc; sc[S_ITERS] = iters + 1;
         if (trial > 0.0) sc[S_DELTA_LAST] = trial;
         sc[S_OBJ] = obj; sc[S_ERR] = err0;
+        sc[S_DBG_THT2] = dbg_tht2; sc[S_DBG_AP2] = dbg_ap2;
+        sc[S_DBG_NAN] = dbg_nan; sc[S_DBG_THT0] = dbg_tht0; sc[S_DBG_PHT0] = dbg_pht0; sc[S_DBG_PHI] = phi; sc[S_DBG_SOC] = use_soc;
+        sc[S_DBG_ALPHA] = alpha; sc[S_DBG_AP] = dbg_ap; sc[S_DBG_THETA] = theta; sc[S_DBG_DPHI] = dbg_dphi;
     }
 }
 
@@ -937,6 +1059,7 @@ static int fill_prob(vc_handle* h, Prob& pr, int B, const double* d_x0, const do
     pr.p = h->params; pr.c = h->cfg;
     pr.B = B; pr.N = h->cfg.N; pr.M = h->cfg.M; pr.H = pr.N + pr.M;
     pr.n_obs = (h->cfg.obstacles && d_obst) ? n_obs : 0;
+    pr.z_init = getenv("VC_ZINIT") ? atof(getenv("VC_ZINIT")) : 0.0;
     pr.x0 = d_x0; pr.kappa = d_kappa; pr.ds = d_ds; pr.obst = d_obst;
     pr.X = pr.U = pr.obj = pr.kkt = nullptr; pr.status = pr.iters = nullptr;
     return 0;
@@ -988,19 +1111,30 @@ int launch_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_k
     const int max_pass = h->cfg.max_iter + 16;
     const bool debug = getenv("VC_DEBUG") != nullptr;
     int pass = 0;
+    const bool prof = h->profiling != 0;
+    size_t ev = 0;
+    auto mark = [&]() {
+        if (!prof) return;
+        if (ev >= h->prof_events.size()) { cudaEvent_t e; cudaEventCreate(&e); h->prof_events.push_back(e); }
+        cudaEventRecord(h->prof_events[ev++], st);
+    };
     for (; pass < max_pass; ++pass) {
+        mark();
         k_eval_st<<<(unsigned)((t_st + 127) / 128), 128, 0, st>>>(pr, ws);
+        mark();
         if (pr.M > 0) k_eval_pm<<<(unsigned)((t_pm + 127) / 128), 128, 0, st>>>(pr, ws);
         cudaMemsetAsync(h->d_active, 0, sizeof(int), st);
+        mark();
         k_step<<<(B + STEP_WARPS - 1) / STEP_WARPS, 32 * STEP_WARPS, 0, st>>>(pr, ws, h->d_active);
+        mark();
         h->launches += pr.M > 0 ? 3 : 2;
         if (debug) {   // VC_DEBUG=1: trace instance 0
             double sc[NSCAL];
             cudaMemcpyAsync(sc, ws.scal(0), sizeof(sc), cudaMemcpyDeviceToHost, st);
             cudaStreamSynchronize(st);
-            fprintf(stderr, "[vc] pass %3d mode %d it %3d mu %.3e sf %.4g obj %.10f err %.3e delta %.2e nfilt %d restarts %d status %d\n",
+            fprintf(stderr, "[vc] pass %3d mode %d it %3d mu %.3e sf %.4g obj %.10f err %.3e delta %.2e nfilt %d restarts %d status %d | alpha %.3e a_p %.3e theta %.3e dphi %.3e nan %d tht0 %.3e pht0 %.6e phi %.6e soc %d tht2 %.3e ap2 %.3e\n",
                     pass, (int)sc[S_MODE], (int)sc[S_ITERS], sc[S_MU], sc[S_SF], sc[S_OBJ], sc[S_ERR], sc[S_DELTA_LAST],
-                    (int)sc[S_NFILT], (int)sc[S_RESTARTS], (int)sc[S_STATUS]);
+                    (int)sc[S_NFILT], (int)sc[S_RESTARTS], (int)sc[S_STATUS], sc[S_DBG_ALPHA], sc[S_DBG_AP], sc[S_DBG_THETA], sc[S_DBG_DPHI], (int)sc[S_DBG_NAN], sc[S_DBG_THT0], sc[S_DBG_PHT0], sc[S_DBG_PHI], (int)sc[S_DBG_SOC], sc[S_DBG_THT2], sc[S_DBG_AP2]);
         }
         if (pass >= 4) {   // finished instances idle; stop as soon as none is left
             cudaMemcpyAsync(h->h_active, h->d_active, sizeof(int), cudaMemcpyDeviceToHost, st);
@@ -1009,8 +1143,28 @@ int launch_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_k
             if (*h->h_active == 0) break;
         }
     }
-    h->last_passes = pass + 1;
+    h->last_passes = pass < max_pass ? pass + 1 : max_pass;
+    if (prof) {
+        cudaStreamSynchronize(st);
+        for (size_t i = 0; i + 3 < ev; i += 4) {
+            float a, b2, c2;
+            cudaEventElapsedTime(&a, h->prof_events[i], h->prof_events[i + 1]);
+            cudaEventElapsedTime(&b2, h->prof_events[i + 1], h->prof_events[i + 2]);
+            cudaEventElapsedTime(&c2, h->prof_events[i + 2], h->prof_events[i + 3]);
+            h->prof_ms[0] += a; h->prof_ms[1] += b2; h->prof_ms[2] += c2;
+            h->prof_launches[0]++; h->prof_launches[1] += pr.M > 0; h->prof_launches[2]++;
+        }
+    }
     return check_cuda(cudaGetLastError(), "nmpc solve");
 }
 
+
+int debug_read(vc_handle* h, int b, int array, double* h_out, int n) {
+    if (!h->d_ws) { set_error("debug_read: no workspace"); return -1; }
+    const int H = h->cfg.N + h->cfg.M;
+    Ws ws; ws.H = H; ws.stride = (size_t)WS_PER_STAGE * H + NSCAL; ws.base = (double*)h->d_ws;
+    const double* src = array < 0 ? ws.scal(b) : ws.arr(b, array);
+    cudaStreamSynchronize(h->stream);
+    return check_cuda(cudaMemcpy(h_out, src, sizeof(double) * n, cudaMemcpyDeviceToHost), "debug_read");
+}
 }  // namespace vc

@@ -224,5 +224,23 @@ class Engine:
                                           kkt.ctypes.data), "vc_nmpc_solve_host")
         return {"obj": obj, "status": status, "iters": iters, "kkt": kkt}
 
+    def set_profiling(self, on: bool):
+        check(self.lib.vc_set_profiling(self._h, 1 if on else 0), "vc_set_profiling")
+
+    def profile(self):
+        """dict(ms=[k_eval_st, k_eval_pm, k_step], launches=[...], last_passes=int) since set_profiling(True)."""
+        ms, ln, lp = (C.c_double * 3)(), (C.c_longlong * 3)(), C.c_int()
+        check(self.lib.vc_get_profile(self._h, C.addressof(ms), C.addressof(ln), C.addressof(lp)), "vc_get_profile")
+        return {"ms": list(ms), "launches": list(ln), "last_passes": lp.value}
+
+    def debug_read(self, b, array, n):
+        out = np.empty(n)
+        check(self.lib.vc_nmpc_debug_read(self._h, int(b), int(array), out.ctypes.data, int(n)), "vc_nmpc_debug_read")
+        return out
+
+    def workspace_bytes(self) -> int:
+        N, M = self.cfg.N, self.cfg.M
+        return int(self.lib.vc_workspace_bytes(self._h))
+
     def launch_count(self) -> int:
         return int(self.lib.vc_launch_count(self._h))
