@@ -73,7 +73,7 @@ constexpr int WS_PER_STAGE = ws_offset(W_COUNT);
 constexpr int NSCAL = 64;
 // scalar block of an instance
 enum Scal { S_MU = 0, S_SF, S_DELTA_LAST, S_THETA0, S_NFILT, S_ACC, S_MODE, S_RESTARTS, S_OBJ, S_ERR, S_ITERS,
-            S_STATUS, S_DBG_ALPHA, S_DBG_AP, S_DBG_THETA, S_DBG_DPHI, S_FILT = 16, S_DBG_NAN = 50, S_DBG_THT0, S_DBG_PHT0, S_DBG_PHI, S_DBG_SOC, S_DBG_THT2, S_DBG_AP2 /* theta[16] */, S_FILP = 32 /* phi[16] */ };
+            S_STATUS, S_DBG_ALPHA, S_DBG_AP, S_DBG_THETA, S_DBG_DPHI, S_FILT = 16, S_DBG_NAN = 50, S_DBG_THT0, S_DBG_PHT0, S_DBG_PHI, S_DBG_SOC, S_DBG_THT2, S_DBG_AP2, S_SHORT /* theta[16] */, S_FILP = 32 /* phi[16] */ };
 constexpr int FILT_MAX = 16;
 enum Mode { MODE_INIT = 0, MODE_STEP = 1, MODE_DONE = 2, MODE_REINIT = 3 };
 
@@ -90,6 +90,8 @@ struct Prob {   // device-side view of one vc_nmpc_solve call
     Params p;
     Cfg c;
     int B, N, M, H, n_obs;
+    int stall_iters;   // consecutive shortened steps before the barrier parameter is forced down
+    double z_cap;      // > 0: initial multipliers min(mu/s, z_cap)
     double z_init;   // > 0: constant initial inequality multipliers (IPOPT warm_start_mult_bound_push); else mu/s
     const double *x0, *kappa, *ds, *obst;
     double *X, *U, *obj, *kkt;
@@ -506,7 +508,7 @@ __device__ void init_slacks(const Prob& pr, const Ws& ws, int b, int lane, doubl
         double *s = ws.at(b, W_S, k), *z = ws.at(b, W_Z, k), *lam = ws.at(b, W_LAM, k);
         for (int j = 0; j < (k < pr.N ? NI_ST : NI_PM); ++j) {
             s[j] = fmax(cr[j], IpmConst::slack_push * fmax(1.0, fabs(cr[j])));
-            z[j] = pr.z_init > 0.0 ? pr.z_init : mu / s[j];
+            z[j] = pr.z_init > 0.0 ? pr.z_init : (pr.z_cap > 0.0 ? fmin(mu / s[j], pr.z_cap) : mu / s[j]);
         }
         for (int i = 0; i < 8; ++i) lam[i] = 0.0;
     }
@@ -897,6 +899,14 @@ __global__ void __launch_bounds__(32 * STEP_WARPS) k_step(Prob pr, Ws ws, int* n
         mu = fmax(mu_floor, fmin(IpmConst::kappa_mu * mu, pow(mu, IpmConst::theta_mu)));
         nfilt = 0;
     }
+    // stall escape (stands in for IPOPT's watchdog): several consecutive heavily shortened steps mean the Newton
+    // model of this barrier problem is poor where the iterate sits; the barrier problem need not be solved
+    // accurately for path following, so move on to the next rung
+    int n_short = (int)sc[S_SHORT];
+    if (n_short >= pr.stall_iters && mu > mu_floor * (1 + 1e-12)) {
+        mu = fmax(mu_floor, fmin(IpmConst::kappa_mu * mu, pow(mu, IpmConst::theta_mu)));
+        nfilt = 0; n_short = 0;
+    }
     const double tau = fmax(IpmConst::tau_min, 1.0 - mu);
     const double theta = m.theta, phi = sf * m.f - mu * m.lns;
     double theta0 = sc[S_THETA0];
@@ -1014,6 +1024,7 @@ __global__ void __launch_bounds__(32 * STEP_WARPS) k_step(Prob pr, Ws ws, int* n
         }
     }
     if (lane == 0) {
+        sc[S_SHORT] = (alpha < 0.05 * dbg_ap && !use_soc) ? n_short + 1 : 0;
         sc[S_MU] = mu; sc[S_NFILT] = nfilt; sc[S_THETA0] = theta0; sc[S_ACC] = acc; sc[S_ITERS] = iters + 1;
         if (trial > 0.0) sc[S_DELTA_LAST] = trial;
         sc[S_OBJ] = obj; sc[S_ERR] = err0;
@@ -1060,6 +1071,8 @@ static int fill_prob(vc_handle* h, Prob& pr, int B, const double* d_x0, const do
     pr.B = B; pr.N = h->cfg.N; pr.M = h->cfg.M; pr.H = pr.N + pr.M;
     pr.n_obs = (h->cfg.obstacles && d_obst) ? n_obs : 0;
     pr.z_init = getenv("VC_ZINIT") ? atof(getenv("VC_ZINIT")) : 0.0;
+    pr.z_cap = getenv("VC_ZCAP") ? atof(getenv("VC_ZCAP")) : 0.0;
+    pr.stall_iters = getenv("VC_STALL") ? atoi(getenv("VC_STALL")) : 4;
     pr.x0 = d_x0; pr.kappa = d_kappa; pr.ds = d_ds; pr.obst = d_obst;
     pr.X = pr.U = pr.obj = pr.kkt = nullptr; pr.status = pr.iters = nullptr;
     return 0;
