@@ -27,7 +27,8 @@ struct vc_handle {
     // NMPC solver workspace
     void* d_ws = nullptr;
     size_t ws_bytes = 0;
-    int* d_active = nullptr;
+    int* d_active = nullptr;   // [2] counters + 2 x [active_cap] compacted instance lists
+    int active_cap = 0;
     int* h_active = nullptr;
     int last_passes = 0;
     // optional per-kernel timing of the solver loop (vc_set_profiling)

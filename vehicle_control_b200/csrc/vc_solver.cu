@@ -73,7 +73,7 @@ constexpr int WS_PER_STAGE = ws_offset(W_COUNT);
 constexpr int NSCAL = 64;
 // scalar block of an instance
 enum Scal { S_MU = 0, S_SF, S_DELTA_LAST, S_THETA0, S_NFILT, S_ACC, S_MODE, S_RESTARTS, S_OBJ, S_ERR, S_ITERS,
-            S_STATUS, S_DBG_ALPHA, S_DBG_AP, S_DBG_THETA, S_DBG_DPHI, S_FILT = 16, S_DBG_NAN = 50, S_DBG_THT0, S_DBG_PHT0, S_DBG_PHI, S_DBG_SOC, S_DBG_THT2, S_DBG_AP2, S_SHORT /* theta[16] */, S_FILP = 32 /* phi[16] */ };
+            S_STATUS, S_DBG_ALPHA, S_DBG_AP, S_DBG_THETA, S_DBG_DPHI, S_FILT = 16, S_NREST = 48, S_DBG_NAN = 50, S_DBG_THT0, S_DBG_PHT0, S_DBG_PHI, S_DBG_SOC, S_DBG_THT2, S_DBG_AP2, S_SHORT /* theta[16] */, S_FILP = 32 /* phi[16] */ };
 constexpr int FILT_MAX = 16;
 enum Mode { MODE_INIT = 0, MODE_STEP = 1, MODE_DONE = 2, MODE_REINIT = 3 };
 
@@ -91,11 +91,16 @@ struct Prob {   // device-side view of one vc_nmpc_solve call
     Cfg c;
     int B, N, M, H, n_obs;
     int stall_iters;   // consecutive shortened steps before the barrier parameter is forced down
+    int max_soc;       // second-order correction steps per iteration (IPOPT max_soc = 4)
+    int restore_iters; // > 0: consecutive shortened steps before the iterate is projected onto the dynamics (restoration)
     double z_cap;      // > 0: initial multipliers min(mu/s, z_cap)
     double z_init;   // > 0: constant initial inequality multipliers (IPOPT warm_start_mult_bound_push); else mu/s
     const double *x0, *kappa, *ds, *obst;
     double *X, *U, *obj, *kkt;
     int *status, *iters;
+    // compacted list of unfinished instances of this pass (written by the previous k_step) and its length
+    const int* act_list;
+    const int* act_count;
 };
 
 // active (differentiated) stage variables
@@ -110,10 +115,12 @@ __device__ __forceinline__ void pair_from_index(int q, int& a, int& b) {   // q 
 
 // ------------------------------------------------------------------------------------------------
 // k_prepare: user layout X[B,8,H], U[B,2,H] (state_prediction / action_prediction) -> stage-major workspace
-__global__ void k_prepare(Prob pr, Ws ws) {
+__global__ void k_prepare(Prob pr, Ws ws, int* list0, int* count0) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= pr.B * pr.H) return;
     const int b = t / pr.H, k = t % pr.H, H = pr.H;
+    if (k == 0) list0[b] = b;
+    if (t == 0) *count0 = pr.B;
     const double* Xb = pr.X + (size_t)b * 8 * H;
     const double* Ub = pr.U + (size_t)b * 2 * H;
     double* y = ws.at(b, W_Y, k);
@@ -140,10 +147,9 @@ __global__ void k_prepare(Prob pr, Ws ws) {
 __global__ void __launch_bounds__(128) k_eval_st(Prob pr, Ws ws) {
     const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const int N = pr.N;
-    if (t >= (long long)pr.B * N * 36) return;
-    const int q = (int)(t % 36), k = (int)((t / 36) % N), b = (int)(t / (36LL * N));
+    if (t >= (long long)(*pr.act_count) * N * 36) return;
+    const int q = (int)(t % 36), k = (int)((t / 36) % N), b = pr.act_list[(int)(t / (36LL * N))];
     const double* sc = ws.scal(b);
-    if (sc[S_MODE] == MODE_DONE) return;
     int ia, ib;
     pair_from_index(q, ia, ib);
     const int va = c_act_st[ia], vb = c_act_st[ib];
@@ -230,10 +236,9 @@ __global__ void __launch_bounds__(128) k_eval_st(Prob pr, Ws ws) {
 __global__ void __launch_bounds__(128) k_eval_pm(Prob pr, Ws ws) {
     const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const int M = pr.M, N = pr.N, H = pr.H;
-    if (t >= (long long)pr.B * M * 15) return;
-    const int q = (int)(t % 15), k = N + (int)((t / 15) % M), b = (int)(t / (15LL * M));
+    if (t >= (long long)(*pr.act_count) * M * 15) return;
+    const int q = (int)(t % 15), k = N + (int)((t / 15) % M), b = pr.act_list[(int)(t / (15LL * M))];
     const double* sc = ws.scal(b);
-    if (sc[S_MODE] == MODE_DONE) return;
     int ia, ib;
     pair_from_index(q, ia, ib);
     const int va = c_act_pm[ia], vb = c_act_pm[ib];
@@ -809,7 +814,7 @@ __device__ void soc_residual(const Prob& pr, const Ws& ws, int b, int lane, doub
 // restoration substitute (oracle/nlp.py NLP.repair): guess-independent, dynamically feasible re-initialisation
 // -- hold the speed (Fx = drag), no steering rate, PointMass Fy follows the centre-line curvature -- with the
 // states re-generated by rolling the models out from x0
-__device__ void repair_rollout(const Prob& pr, const Ws& ws, int b) {
+__device__ void repair_rollout(const Prob& pr, const Ws& ws, int b, bool neutral = true) {
     const int H = pr.H, N = pr.N;
     const double* kap = pr.kappa + (size_t)b * H;
     const double* dsb = pr.ds + (size_t)b * H;
@@ -817,8 +822,7 @@ __device__ void repair_rollout(const Prob& pr, const Ws& ws, int b) {
     for (int i = 0; i < 8; ++i) y[i] = pr.x0[(size_t)b * 8 + i];
     for (int k = 0; k < N; ++k) {
         y = ws.at(b, W_Y, k);
-        y[YFX] = pr.p.Frr + pr.p.Cd * y[IUX] * y[IUX];
-        y[YW] = 0.0;
+        if (neutral) { y[YFX] = pr.p.Frr + pr.p.Cd * y[IUX] * y[IUX]; y[YW] = 0.0; }
         if (k < N - 1) st_rk4<true>(pr.p, y, y + 8, kap[k], dsb[k], ws.at(b, W_Y, k + 1));
     }
     if (pr.M > 0) {
@@ -826,8 +830,7 @@ __device__ void repair_rollout(const Prob& pr, const Ws& ws, int b) {
         st_switch(pr.p, ws.at(b, W_Y, N - 1), ws.at(b, W_Y, N), T);
         for (int k = N; k < H; ++k) {
             y = ws.at(b, W_Y, k);
-            y[QFX] = pr.p.Frr + pr.p.Cd * y[QV] * y[QV];
-            y[QFY] = pr.p.m * y[QV] * y[QV] * kap[k];
+            if (neutral) { y[QFX] = pr.p.Frr + pr.p.Cd * y[QV] * y[QV]; y[QFY] = pr.p.m * y[QV] * y[QV] * kap[k]; }
             if (k < H - 1) pm_euler<true>(pr.p, y, y + 5, kap[k], dsb[k], ws.at(b, W_Y, k + 1));
         }
     }
@@ -848,16 +851,10 @@ __device__ void repair_rollout(const Prob& pr, const Ws& ws, int b) {
 
 // ------------------------------------------------------------------------------------------------
 // k_step: one interior-point iteration of every unfinished instance (one warp each)
-__global__ void __launch_bounds__(32 * STEP_WARPS) k_step(Prob pr, Ws ws, int* n_active) {
-    __shared__ WarpSm s_all[STEP_WARPS];
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int b = blockIdx.x * STEP_WARPS + wid;
-    if (b >= pr.B) return;
-    WarpSm& sm = s_all[wid];
+__device__ void step_instance(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int lane) {
     double* sc = ws.scal(b);
     const int mode = (int)sc[S_MODE];
     if (mode == MODE_DONE) return;
-    if (lane == 0) atomicAdd(n_active, 1);
     const int H = pr.H, N = pr.N, M = pr.M;
     const Cfg& c = pr.c;
     const Measures m = finish_gradients(pr, ws, b, lane);
@@ -906,6 +903,23 @@ __global__ void __launch_bounds__(32 * STEP_WARPS) k_step(Prob pr, Ws ws, int* n
     if (n_short >= pr.stall_iters && mu > mu_floor * (1 + 1e-12)) {
         mu = fmax(mu_floor, fmin(IpmConst::kappa_mu * mu, pow(mu, IpmConst::theta_mu)));
         nfilt = 0; n_short = 0;
+    }
+    // feasibility restoration substitute: a run of heavily shortened steps at an infeasible iterate means the
+    // linearisation is poor there (IPOPT would end up in its restoration phase); project the iterate onto the
+    // dynamics manifold by rolling the models out from x0 under the CURRENT controls and restart the barrier
+    // problem from that point (same mu, cleared filter)
+    if (pr.restore_iters > 0 && n_short >= pr.restore_iters && (int)sc[S_NREST] < 3 && m.theta > 1e-6) {
+        __syncwarp();
+        if (lane == 0) {
+            repair_rollout(pr, ws, b, false);
+            sc[S_NREST] += 1.0; sc[S_MODE] = MODE_REINIT; sc[S_SHORT] = 0; sc[S_ITERS] = iters + 1; sc[S_MU] = mu;
+        }
+        for (int k = lane; k < H; k += 32) {
+            double *lam = ws.at(b, W_LAM, k), *s = ws.at(b, W_S, k), *z = ws.at(b, W_Z, k);
+            for (int i = 0; i < 8; ++i) lam[i] = 0.0;
+            for (int j = 0; j < 10; ++j) { s[j] = 1.0; z[j] = 0.0; }
+        }
+        return;
     }
     const double tau = fmax(IpmConst::tau_min, 1.0 - mu);
     const double theta = m.theta, phi = sf * m.f - mu * m.lns;
@@ -960,10 +974,10 @@ __global__ void __launch_bounds__(32 * STEP_WARPS) k_step(Prob pr, Ws ws, int* n
             if (okv && acceptable(alpha, tht, sf * ft - mu * lnt, dphi, augment)) accepted = true;
             // ---- second-order correction (IPOPT Alg. A-5.5 .. A-5.9): first trial step rejected and infeasibility
             // not reduced -> re-solve with c_soc = alpha c(x) + c(x + alpha d), at most 4 times
-            if (!accepted && bt == 0 && okv && tht >= theta) {
+            if (!accepted && bt == 0 && okv && tht >= theta && pr.max_soc > 0) {
                 soc_residual(pr, ws, b, lane, alpha, false, true);
                 double theta_soc_old = theta;
-                for (int ps = 0; ps < 4; ++ps) {
+                for (int ps = 0; ps < pr.max_soc; ++ps) {
                     if (!riccati(pr, ws, sm, b, lane, mu, trial, true)) break;
                     double a_p2, a_d2, dphi2, ft2, tht2, lnt2;
                     slack_directions(pr, ws, b, lane, mu, tau, true, a_p2, a_d2, dphi2);
@@ -1034,6 +1048,18 @@ __global__ void __launch_bounds__(32 * STEP_WARPS) k_step(Prob pr, Ws ws, int* n
     }
 }
 
+__global__ void __launch_bounds__(32 * STEP_WARPS) k_step(Prob pr, Ws ws, int* next_list, int* next_count) {
+    __shared__ WarpSm s_all[STEP_WARPS];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int i = blockIdx.x * STEP_WARPS + wid;
+    if (i >= *pr.act_count) return;
+    const int b = pr.act_list[i];
+    step_instance(pr, ws, s_all[wid], b, lane);
+    __syncwarp();
+    // survivors form the next pass's compacted list (their order does not influence any instance's result)
+    if (lane == 0 && ws.scal(b)[S_MODE] != (double)MODE_DONE) next_list[atomicAdd(next_count, 1)] = b;
+}
+
 // k_nmpc_eval: objective / max equality violation / min inequality margin of given trajectories (no solve)
 __global__ void __launch_bounds__(128) k_nmpc_eval(Prob pr, const double* X, const double* U, double* out) {
     const int lane = threadIdx.x & 31;
@@ -1073,8 +1099,11 @@ static int fill_prob(vc_handle* h, Prob& pr, int B, const double* d_x0, const do
     pr.z_init = getenv("VC_ZINIT") ? atof(getenv("VC_ZINIT")) : 0.0;
     pr.z_cap = getenv("VC_ZCAP") ? atof(getenv("VC_ZCAP")) : 0.0;
     pr.stall_iters = getenv("VC_STALL") ? atoi(getenv("VC_STALL")) : 4;
+    pr.max_soc = getenv("VC_MAXSOC") ? atoi(getenv("VC_MAXSOC")) : 4;
+    pr.restore_iters = getenv("VC_RESTORE") ? atoi(getenv("VC_RESTORE")) : 0;
     pr.x0 = d_x0; pr.kappa = d_kappa; pr.ds = d_ds; pr.obst = d_obst;
     pr.X = pr.U = pr.obj = pr.kkt = nullptr; pr.status = pr.iters = nullptr;
+    pr.act_list = pr.act_count = nullptr;
     return 0;
 }
 
@@ -1110,17 +1139,24 @@ int launch_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_k
         if (rc) return rc;
         h->ws_bytes = bytes;
     }
-    if (!h->d_active) {
-        rc = check_cuda(cudaMalloc(&h->d_active, sizeof(int)), "cudaMalloc(active)");
+    if (B > h->active_cap) {   // two ping-pong index lists [B] + two counters
+        cudaFree(h->d_active);
+        h->d_active = nullptr; h->active_cap = 0;
+        rc = check_cuda(cudaMalloc(&h->d_active, sizeof(int) * (2 * (size_t)B + 2)), "cudaMalloc(active lists)");
         if (rc) return rc;
+        h->active_cap = B;
+    }
+    if (!h->h_active) {
         rc = check_cuda(cudaMallocHost(&h->h_active, sizeof(int)), "cudaMallocHost(active)");
         if (rc) return rc;
     }
+    int* lists[2] = {h->d_active + 2, h->d_active + 2 + h->active_cap};
+    int* counts[2] = {h->d_active, h->d_active + 1};
     ws.base = (double*)h->d_ws;
     cudaStream_t st = h->stream;
-    k_prepare<<<(B * pr.H + 127) / 128, 128, 0, st>>>(pr, ws);
+    k_prepare<<<(B * pr.H + 127) / 128, 128, 0, st>>>(pr, ws, lists[0], counts[0]);
     h->launches++;
-    const long long t_st = (long long)B * pr.N * 36, t_pm = (long long)B * pr.M * 15;
+    int cur = 0, n_act = B;
     const int max_pass = h->cfg.max_iter + 16;
     const bool debug = getenv("VC_DEBUG") != nullptr;
     int pass = 0;
@@ -1132,14 +1168,18 @@ int launch_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_k
         cudaEventRecord(h->prof_events[ev++], st);
     };
     for (; pass < max_pass; ++pass) {
+        // grids are sized by the last count read back (an upper bound); the kernels read the exact count on the device
+        const long long t_st = (long long)n_act * pr.N * 36, t_pm = (long long)n_act * pr.M * 15;
+        pr.act_list = lists[cur]; pr.act_count = counts[cur];
         mark();
         k_eval_st<<<(unsigned)((t_st + 127) / 128), 128, 0, st>>>(pr, ws);
         mark();
         if (pr.M > 0) k_eval_pm<<<(unsigned)((t_pm + 127) / 128), 128, 0, st>>>(pr, ws);
-        cudaMemsetAsync(h->d_active, 0, sizeof(int), st);
+        cudaMemsetAsync(counts[1 - cur], 0, sizeof(int), st);
         mark();
-        k_step<<<(B + STEP_WARPS - 1) / STEP_WARPS, 32 * STEP_WARPS, 0, st>>>(pr, ws, h->d_active);
+        k_step<<<(n_act + STEP_WARPS - 1) / STEP_WARPS, 32 * STEP_WARPS, 0, st>>>(pr, ws, lists[1 - cur], counts[1 - cur]);
         mark();
+        cur = 1 - cur;
         h->launches += pr.M > 0 ? 3 : 2;
         if (debug) {   // VC_DEBUG=1: trace instance 0
             double sc[NSCAL];
@@ -1149,11 +1189,12 @@ int launch_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_k
                     pass, (int)sc[S_MODE], (int)sc[S_ITERS], sc[S_MU], sc[S_SF], sc[S_OBJ], sc[S_ERR], sc[S_DELTA_LAST],
                     (int)sc[S_NFILT], (int)sc[S_RESTARTS], (int)sc[S_STATUS], sc[S_DBG_ALPHA], sc[S_DBG_AP], sc[S_DBG_THETA], sc[S_DBG_DPHI], (int)sc[S_DBG_NAN], sc[S_DBG_THT0], sc[S_DBG_PHT0], sc[S_DBG_PHI], (int)sc[S_DBG_SOC], sc[S_DBG_THT2], sc[S_DBG_AP2]);
         }
-        if (pass >= 4) {   // finished instances idle; stop as soon as none is left
-            cudaMemcpyAsync(h->h_active, h->d_active, sizeof(int), cudaMemcpyDeviceToHost, st);
+        if (pass >= 3) {   // no instance can finish before its third pass (init, >= 1 step, convergence test)
+            cudaMemcpyAsync(h->h_active, counts[cur], sizeof(int), cudaMemcpyDeviceToHost, st);
             rc = check_cuda(cudaStreamSynchronize(st), "nmpc iteration");
             if (rc) return rc;
-            if (*h->h_active == 0) break;
+            n_act = *h->h_active;
+            if (n_act == 0) break;
         }
     }
     h->last_passes = pass < max_pass ? pass + 1 : max_pass;
@@ -1165,6 +1206,7 @@ int launch_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_k
             cudaEventElapsedTime(&b2, h->prof_events[i + 1], h->prof_events[i + 2]);
             cudaEventElapsedTime(&c2, h->prof_events[i + 2], h->prof_events[i + 3]);
             h->prof_ms[0] += a; h->prof_ms[1] += b2; h->prof_ms[2] += c2;
+            if (getenv("VC_PASS_TRACE")) fprintf(stderr, "[vc] pass %3zu eval_st %.3f eval_pm %.3f step %.3f ms\n", i / 4, a, b2, c2);
             h->prof_launches[0]++; h->prof_launches[1] += pr.M > 0; h->prof_launches[2]++;
         }
     }
