@@ -37,6 +37,7 @@ def parse():
     ap.add_argument("--batch", type=int, default=0, help="instances per GPU (0 = config default)")
     ap.add_argument("--e2e-batch", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--lap-cache", default=None, help="npz file to save/load the untimed warm-start lap (profiling runs)")
     return ap.parse_args()
 
 

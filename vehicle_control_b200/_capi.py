@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libvc_b200.so")
+LIB_PATH = os.environ.get("VC_LIB_PATH") or os.path.join(_HERE, "libvc_b200.so")   # VC_LIB_PATH: tuning builds
 
 D = C.c_double
 PD = C.c_void_p  # device or host pointers are passed as raw addresses

@@ -22,54 +22,71 @@
 namespace vc {
 
 // ------------------------------------------------------------------------------------------------
-// per-instance workspace (global memory, one contiguous slab per instance so that a warp streams it)
+// per-instance workspace (global memory): one contiguous slab per instance made of H stage RECORDS of
+// WS_PER_STAGE doubles each, followed by the scalar block.  Inside a record the arrays the Riccati sweep streams
+// come first and are contiguous (backward sweep: [0, WS_BWD); forward sweep: AB and [WS_FWD0, WS_FWD1)), so that a
+// warp stages the next stage's block in shared memory with 16-byte cp.async copies while it works on the current one.
 enum WsArray {
-    W_Y = 0,     // [H][10] stage variables (x,u); PointMass stages use 7
-    W_LAM,       // [H][8]  multiplier of the equality that defines x_k (k=0: initial state)
-    W_S,         // [H][10] slacks of the stage inequalities
-    W_Z,         // [H][10] their multipliers
-    W_HC,        // [H][36] condensed Hessian block, packed lower triangle over the ACTIVE stage variables
-    W_AB,        // [H][80] d(next state)/d(active vars): [i][a] stride 8; switch stage: row 5 = grad T
-    W_JC,        // [H][80] inequality Jacobian [j][a] stride 8
-    W_RD,        // [H][10] dual infeasibility  (eval: active entries; step: s, t, slew, obstacle parts)
-    W_GF,        // [H][10] scaled objective gradient
-    W_V1,        // [H][10] Jc^T (1/s)
-    W_V2,        // [H][10] Jc^T (z c / s)
-    W_GRES,      // [H][8]  equality residual of the row block that defines x_k
-    W_CRES,      // [H][10] inequality values c(y_k)
-    W_FST,       // [H][1]  stage cost (unscaled; AD part only)
-    W_OBS,       // [H][6]  obstacle term: value, d/ds, d/dey, ss, s-ey, ey-ey
-    W_DY,        // [H][10] primal direction
-    W_DLAM,      // [H][8]
-    W_DSL,       // [H][10]
-    W_DZ,        // [H][10]
-    W_PM,        // [H][100] Riccati cost-to-go Hessians
-    W_PV,        // [H][10]
-    W_KM,        // [H][24]  feedback gains K[2][10], kff[2]
-    W_GT,        // [H][8]   equality residual at the last trial point
-    W_CT,        // [H][10]  inequality values at the last trial point
-    W_GS,        // [H][8]   second-order-correction residuals (equalities)
-    W_CS,        // [H][10]  second-order-correction residuals (c - s rows)
-    W_DY2,       // [H][10]  corrected direction
-    W_DLAM2,     // [H][8]
-    W_DSL2,      // [H][10]
-    W_DZ2,       // [H][10]
+    W_HC = 0,    // [36] condensed Hessian block, packed lower triangle over the ACTIVE stage variables
+    W_AB,        // [80] d(next state)/d(active vars): [i][a] stride 8; switch stage: row 5 = grad T, [48] = T
+    W_RD,        // [10] dual infeasibility  (eval: active entries; step: s, t, slew, obstacle parts)
+    W_V1,        // [10] Jc^T (1/s)
+    W_V2,        // [10] Jc^T (z c / s)
+    W_OBS,       // [8]  obstacle term: value, d/ds, d/dey, ss, s-ey, ey-ey; [6],[7] = slew weights tying u_k to u_{k-1}
+    W_GRES,      // [8]  equality residual of the row block that defines x_k
+    W_KM,        // [24] feedback gains K[2][10], kff[2]
+    W_PV,        // [10] Riccati cost-to-go gradient
+    W_PM,        // [100] Riccati cost-to-go Hessian
+    W_Y,         // [10] stage variables (x,u); PointMass stages use 7
+    W_LAM,       // [8]  multiplier of the equality that defines x_k (k=0: initial state)
+    W_S,         // [10] slacks of the stage inequalities
+    W_Z,         // [10] their multipliers
+    W_JC,        // [80] inequality Jacobian [j][a] stride 8
+    W_GF,        // [10] scaled objective gradient
+    W_CRES,      // [10] inequality values c(y_k)
+    W_FST,       // [1]  stage cost (unscaled; AD part only)
+    W_PAD,       // [1]  keeps every record 16-byte aligned
+    W_DY,        // [10] primal direction
+    W_DLAM,      // [8]
+    W_DSL,       // [10]
+    W_DZ,        // [10]
+    W_GT,        // [8]   equality residual at the last trial point
+    W_CT,        // [10]  inequality values at the last trial point
+    W_GS,        // [8]   second-order-correction residuals (equalities)
+    W_CS,        // [10]  second-order-correction residuals (c - s rows)
+    W_DY2,       // [10]  corrected direction
+    W_DLAM2,     // [8]
+    W_DSL2,      // [10]
+    W_DZ2,       // [10]
     W_COUNT
 };
-__host__ __device__ constexpr int ws_width(int a) {
-    return a == W_Y ? 10 : a == W_LAM ? 8 : a == W_S ? 10 : a == W_Z ? 10 : a == W_HC ? 36 : a == W_AB ? 80
-         : a == W_JC ? 80 : a == W_RD ? 10 : a == W_GF ? 10 : a == W_V1 ? 10 : a == W_V2 ? 10 : a == W_GRES ? 8
-         : a == W_CRES ? 10 : a == W_FST ? 1 : a == W_OBS ? 6 : a == W_DY ? 10 : a == W_DLAM ? 8 : a == W_DSL ? 10
-         : a == W_DZ ? 10 : a == W_PM ? 100 : a == W_PV ? 10 : a == W_KM ? 24
-         : a == W_GT ? 8 : a == W_CT ? 10 : a == W_GS ? 8 : a == W_CS ? 10 : a == W_DY2 ? 10 : a == W_DLAM2 ? 8
-         : a == W_DSL2 ? 10 : a == W_DZ2 ? 10 : 0;
-}
-__host__ __device__ constexpr int ws_offset(int a) {   // offset in doubles PER STAGE before array a
+struct WsTable { int width[W_COUNT + 1]; int off[W_COUNT + 1]; };
+constexpr WsTable make_ws_table() {
+    WsTable t{};
+    const int w[W_COUNT] = {36, 80, 10, 10, 10, 8, 8, 24, 10, 100, 10, 8, 10, 10, 80, 10, 10, 1, 1,
+                            10, 8, 10, 10, 8, 10, 8, 10, 10, 8, 10, 10};
     int o = 0;
-    for (int i = 0; i < a; ++i) o += ws_width(i);
-    return o;
+    for (int i = 0; i < W_COUNT; ++i) { t.width[i] = w[i]; t.off[i] = o; o += w[i]; }
+    t.width[W_COUNT] = 0; t.off[W_COUNT] = o;
+    return t;
 }
+constexpr WsTable WS_TABLE = make_ws_table();
+__device__ __constant__ int c_ws_off[W_COUNT + 1] = {
+    WS_TABLE.off[0], WS_TABLE.off[1], WS_TABLE.off[2], WS_TABLE.off[3], WS_TABLE.off[4], WS_TABLE.off[5], WS_TABLE.off[6],
+    WS_TABLE.off[7], WS_TABLE.off[8], WS_TABLE.off[9], WS_TABLE.off[10], WS_TABLE.off[11], WS_TABLE.off[12],
+    WS_TABLE.off[13], WS_TABLE.off[14], WS_TABLE.off[15], WS_TABLE.off[16], WS_TABLE.off[17], WS_TABLE.off[18],
+    WS_TABLE.off[19], WS_TABLE.off[20], WS_TABLE.off[21], WS_TABLE.off[22], WS_TABLE.off[23], WS_TABLE.off[24],
+    WS_TABLE.off[25], WS_TABLE.off[26], WS_TABLE.off[27], WS_TABLE.off[28], WS_TABLE.off[29], WS_TABLE.off[30],
+    WS_TABLE.off[31]};
+constexpr int ws_width(int a) { return WS_TABLE.width[a]; }
+constexpr int ws_offset(int a) { return WS_TABLE.off[a]; }   // offset inside a stage record
 constexpr int WS_PER_STAGE = ws_offset(W_COUNT);
+constexpr int WS_BWD = ws_offset(W_KM);       // [0, WS_BWD): what the backward sweep reads of a stage
+constexpr int WS_FWD0 = ws_offset(W_GRES);    // forward sweep: AB block and [WS_FWD0, WS_FWD1)
+constexpr int WS_FWD1 = ws_offset(W_Y);
+static_assert(WS_PER_STAGE % 2 == 0 && WS_BWD % 2 == 0 && WS_FWD0 % 2 == 0 && WS_FWD1 % 2 == 0 &&
+              ws_offset(W_AB) % 2 == 0 && ws_offset(W_RD) % 2 == 0, "16-byte alignment of the staged blocks");
+static_assert(W_COUNT == 31, "update make_ws_table / c_ws_off");
 constexpr int NSCAL = 64;
 // scalar block of an instance
 enum Scal { S_MU = 0, S_SF, S_DELTA_LAST, S_THETA0, S_NFILT, S_ACC, S_MODE, S_RESTARTS, S_OBJ, S_ERR, S_ITERS,
@@ -81,8 +98,14 @@ struct Ws {
     double* base;
     int H;
     size_t stride;   // doubles per instance
-    __host__ __device__ double* arr(int b, int a) const { return base + (size_t)b * stride + (size_t)ws_offset(a) * H; }
-    __host__ __device__ double* at(int b, int a, int k) const { return arr(b, a) + (size_t)k * ws_width(a); }
+    __host__ __device__ double* rec(int b, int k) const { return base + (size_t)b * stride + (size_t)k * WS_PER_STAGE; }
+    __host__ __device__ double* at(int b, int a, int k) const {
+#if defined(__CUDA_ARCH__)
+        return rec(b, k) + c_ws_off[a];
+#else
+        return rec(b, k) + ws_offset(a);
+#endif
+    }
     __host__ __device__ double* scal(int b) const { return base + (size_t)b * stride + (size_t)WS_PER_STAGE * H; }
 };
 
@@ -144,7 +167,10 @@ __global__ void k_prepare(Prob pr, Ws ws, int* list0, int* count0) {
 // ------------------------------------------------------------------------------------------------
 // k_eval_st: one thread per (instance, SingleTrack stage, pair (a,b) of active variables).  The stage's
 // Lagrangian terms are evaluated once in hyper-dual arithmetic seeded along (a,b): values, d/da, d/db, d2/dadb.
-__global__ void __launch_bounds__(128) k_eval_st(Prob pr, Ws ws) {
+#ifndef VC_EVAL_MINBLOCKS
+#define VC_EVAL_MINBLOCKS 1
+#endif
+__global__ void __launch_bounds__(128, VC_EVAL_MINBLOCKS) k_eval_st(Prob pr, Ws ws) {
     const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const int N = pr.N;
     if (t >= (long long)(*pr.act_count) * N * 36) return;
@@ -353,7 +379,7 @@ __device__ __forceinline__ double slew_prev(const Prob& pr, const Ws& ws, int b,
 // Values of one stage at a trial point (plain doubles): objective share, constraint violation share,
 // log-barrier share.  y = stage variables, yn = next stage's (nullptr at the last stage), sl = trial slacks.
 struct StageVal { double f, theta, lns, gmax, cmin; };
-__device__ StageVal stage_trial(const Prob& pr, int b, int k, const double* y, const double* yn, const double* sl,
+__device__ __noinline__ StageVal stage_trial(const Prob& pr, int b, int k, const double* y, const double* yn, const double* sl,
                                 double* og0 = nullptr, double* ogn = nullptr, double* oc = nullptr) {
     StageVal o{0.0, 0.0, 0.0, 0.0, INFINITY};
     const int H = pr.H, N = pr.N;
@@ -409,13 +435,21 @@ __device__ StageVal stage_trial(const Prob& pr, int b, int k, const double* y, c
 
 // ------------------------------------------------------------------------------------------------
 // k_step building blocks (one warp per instance; `lane` strides over stages or matrix entries)
-constexpr int STEP_WARPS = 4;
-struct WarpSm {
+#ifndef VC_STEP_WARPS
+#define VC_STEP_WARPS 4
+#endif
+#ifndef VC_STEP_MINBLOCKS
+#define VC_STEP_MINBLOCKS 1
+#endif
+constexpr int STEP_WARPS = VC_STEP_WARPS;
+constexpr int RING_DOUBLES = 672;
+struct __align__(16) WarpSm {
     double P[100];     // cost-to-go Hessian of the NEXT stage (stride 10)
     double M[120];     // [A~ B~] of the lifted transition (stride 12)
     double PMm[120];   // P * M
     double G[144];     // stage Hessian + M^T P M (stride 12), order [x | p | u]
     double p[12], r[12], g[12], x[12], tv[12], K[24];
+    double ring[RING_DOUBLES];   // stage blocks staged by cp.async ahead of the Riccati sweeps
 };
 
 struct Measures { double rdmax, prim, sumlam, sumz, theta, f, lns, gfmax; };
@@ -429,7 +463,7 @@ struct IpmConst {
 
 // completes the gradients that k_eval left open (s, t, obstacle and control-continuity parts) and reduces
 // the error measures over the warp
-__device__ Measures finish_gradients(const Prob& pr, const Ws& ws, int b, int lane) {
+__device__ __noinline__ Measures finish_gradients(const Prob& pr, const Ws& ws, int b, int lane) {
     const int H = pr.H, N = pr.N;
     const double* sc = ws.scal(b);
     const double sf = sc[S_SF];
@@ -446,6 +480,7 @@ __device__ Measures finish_gradients(const Prob& pr, const Ws& ws, int b, int la
         ob[0] = ov; ob[1] = og[0]; ob[2] = og[1]; ob[3] = oh[0]; ob[4] = oh[1]; ob[5] = oh[2];
         double p0, p1, c0, c1, g0 = 0.0, g1 = 0.0, fsl = 0.0;
         slew_weights(pr, dsb, k - 1, p0, p1);
+        ob[6] = p0; ob[7] = p1;
         slew_weights(pr, dsb, k, c0, c1);
         const double u0 = y[d.nu_off], u1 = y[d.nu_off + 1];
         if (k > 0) {
@@ -547,18 +582,54 @@ __device__ void finalize(const Prob& pr, const Ws& ws, int b, int lane, int stat
 // position of stage variable i of stage k inside the Riccati ordering [x | p | u]
 __device__ __forceinline__ int gpos(const Dims& d, int i) { return i < d.nu_off ? i : d.n + (i - d.nu_off); }
 
-// builds M = [A~ B~] (rows: lifted next state, cols: [x | p | u] of stage k) and r~ in shared memory
-__device__ void build_transition(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int lane, int k, const Dims& d,
-                                 const Dims& dn, int a_gres) {
-    const int nn = d.n + 2;
-    for (int e = lane; e < dn.n * 12; e += 32) sm.M[e] = 0.0;
-    __syncwarp();
-    const double* ab = ws.at(b, W_AB, k);
-    const int na = d.st ? 8 : 5;
-    for (int e = lane; e < dn.nx * na; e += 32) {
-        const int i = e / na, a = e % na;
-        const int yi = d.st ? c_act_st[a] : c_act_pm[a];
-        sm.M[i * 12 + gpos(d, yi)] = ab[i * 8 + a];
+// ---- cp.async staging of stage blocks (16-byte copies, L2 -> shared memory, bypassing L1)
+__device__ __forceinline__ void cp_async16(double* smem, const double* gmem) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+
+// offsets inside a stage record / inside the staged copies
+constexpr int O_HC = ws_offset(W_HC), O_AB = ws_offset(W_AB), O_RD = ws_offset(W_RD), O_V1 = ws_offset(W_V1),
+              O_V2 = ws_offset(W_V2), O_OBS = ws_offset(W_OBS), O_GRES = ws_offset(W_GRES);
+constexpr int BWD_DEPTH = 4, BWD_SLOT = WS_BWD + 2;                 // backward ring: 4 slots of the [0, WS_BWD) block
+constexpr int FWD_DEPTH = 3, FWD_SLOT = 80 + (WS_FWD1 - WS_FWD0);   // forward ring: AB | GRES KM PV PM, compacted
+constexpr int F_AB = 0, F_GRES = 80, F_KM = F_GRES + 8, F_PV = F_KM + 24, F_PM = F_PV + 10;
+static_assert(BWD_DEPTH * BWD_SLOT <= RING_DOUBLES && FWD_DEPTH * FWD_SLOT <= RING_DOUBLES, "ring too small");
+static_assert(BWD_SLOT % 2 == 0 && FWD_SLOT % 2 == 0, "slot alignment");
+
+__device__ __forceinline__ void stage_fetch_bwd(const Ws& ws, WarpSm& sm, int b, int k, int lane) {
+    if (k >= 0) {
+        const double* rec = ws.rec(b, k);
+        double* dst = sm.ring + (k % BWD_DEPTH) * BWD_SLOT;
+        for (int c = lane; c < WS_BWD / 2; c += 32) cp_async16(dst + 2 * c, rec + 2 * c);
+    }
+    cp_async_commit();
+}
+__device__ __forceinline__ void stage_fetch_fwd(const Ws& ws, WarpSm& sm, int b, int k, int H, int lane) {
+    if (k < H) {
+        const double* rec = ws.rec(b, k);
+        double* dst = sm.ring + (k % FWD_DEPTH) * FWD_SLOT;
+        for (int c = lane; c < 40; c += 32) cp_async16(dst + F_AB + 2 * c, rec + O_AB + 2 * c);
+        for (int c = lane; c < (WS_FWD1 - WS_FWD0) / 2; c += 32) cp_async16(dst + F_GRES + 2 * c, rec + WS_FWD0 + 2 * c);
+    }
+    cp_async_commit();
+}
+
+// builds M = [A~ B~] (rows: lifted next state, cols: [x | p | u] of stage k) in shared memory from the staged
+// dynamics Jacobian `ab` ([i][a] stride 8).  M must have been zeroed (and the warp synchronised) before.
+__device__ __forceinline__ void scatter_transition(WarpSm& sm, const double* ab, int lane, const Dims& d, const Dims& dn) {
+    if (d.st) {
+        for (int e = lane; e < dn.nx * 8; e += 32) {
+            const int i = e >> 3, a = e & 7;
+            sm.M[i * 12 + gpos(d, c_act_st[a])] = ab[e];
+        }
+    } else {
+        for (int e = lane; e < dn.nx * 5; e += 32) {
+            const int i = (e * 13108) >> 16, a = e - i * 5;   // e / 5, e % 5 for e < 64
+            sm.M[i * 12 + gpos(d, c_act_pm[a])] = ab[i * 8 + a];
+        }
     }
     if (lane == 0) {   // s and t pass through with unit derivative
         sm.M[(dn.st ? IS : QS) * 12 + (d.st ? IS : QS)] = 1.0;
@@ -566,43 +637,47 @@ __device__ void build_transition(const Prob& pr, const Ws& ws, WarpSm& sm, int b
         sm.M[dn.nx * 12 + d.n] = 1.0;                              // p0 <- Fx_k
         if (dn.np > 1 && !d.st) sm.M[(dn.nx + 1) * 12 + d.n + 1] = 1.0;   // p1 <- Fy_k
     }
-    if (dn.np > 1 && d.st && lane < 8)                             // p1 <- T(y_{N-1}) = Fy_f + Fy_r
-        sm.M[(dn.nx + 1) * 12 + gpos(d, c_act_st[lane])] = ab[5 * 8 + lane];
-    if (lane < dn.n) sm.r[lane] = lane < dn.nx ? -ws.at(b, a_gres, k + 1)[lane] : 0.0;
-    (void)nn;
-    __syncwarp();
+    if (dn.np > 1 && d.st && lane >= 8 && lane < 16)               // p1 <- T(y_{N-1}) = Fy_f + Fy_r
+        sm.M[(dn.nx + 1) * 12 + gpos(d, c_act_st[lane - 8])] = ab[5 * 8 + lane - 8];
 }
 
 // Backward Riccati sweep + forward substitution of the condensed KKT system
 //   [Hc + delta I  Jg^T] [dw  ]   [-(rd - mu v1 + v2)]
 //   [Jg            0   ] [dlam] = [-g                ]
 // Returns false when some reduced Hessian block is not positive definite (wrong inertia for this delta).
-__device__ bool riccati(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int lane, double mu, double delta, bool soc) {
+// The per-stage blocks are streamed through a shared-memory ring with cp.async, several stages ahead of the math.
+__device__ __noinline__ bool riccati(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int lane, double mu, double delta, bool soc) {
     const int H = pr.H, N = pr.N;
     // second-order correction: same matrix, residuals replaced by the accumulated c_soc (IPOPT 2.4 / Alg. A-5.7)
     const int a_gres = soc ? W_GS : W_GRES, a_dy = soc ? W_DY2 : W_DY, a_dlam = soc ? W_DLAM2 : W_DLAM;
     const double sf = ws.scal(b)[S_SF];
-    const double* dsb = pr.ds + (size_t)b * H;
     bool ok = true;
-    for (int k = H - 1; k >= 0 && ok; --k) {
+    __syncwarp();
+    for (int j = 1; j < BWD_DEPTH; ++j) stage_fetch_bwd(ws, sm, b, H - j, lane);
+    for (int k = H - 1; k >= 0; --k) {
+        stage_fetch_bwd(ws, sm, b, k - (BWD_DEPTH - 1), lane);
         const Dims d = stage_dims(N, k);
         const int n = d.n, nn = n + 2;
+        const int rcp_nn = 65536 / nn + 1, rcp_n = 65536 / n + 1;
         for (int e = lane; e < 144; e += 32) sm.G[e] = 0.0;
+        for (int e = lane; e < 120; e += 32) sm.M[e] = 0.0;
+        cp_async_wait<BWD_DEPTH - 1>();
         __syncwarp();
+        const double* sb = sm.ring + (k % BWD_DEPTH) * BWD_SLOT;
         {   // stage Hessian block over the active variables
-            const double* hc = ws.at(b, W_HC, k);
             const int npair = d.st ? 36 : 15;
             for (int q = lane; q < npair; q += 32) {
-                int ia, ib;
-                pair_from_index(q, ia, ib);
+                int ia = (int)((sqrtf(8.0f * q + 1.0f) - 1.0f) * 0.5f);
+                if ((ia + 1) * (ia + 2) / 2 <= q) ++ia;
+                if (ia * (ia + 1) / 2 > q) --ia;
+                const int ib = q - ia * (ia + 1) / 2;
                 const int pa = gpos(d, d.st ? c_act_st[ia] : c_act_pm[ia]), pb = gpos(d, d.st ? c_act_st[ib] : c_act_pm[ib]);
-                const double v = hc[q];
+                const double v = sb[O_HC + q];
                 sm.G[pa * 12 + pb] = v;
                 sm.G[pb * 12 + pa] = v;
             }
-            const double *rd = ws.at(b, W_RD, k), *v1 = ws.at(b, W_V1, k), *v2 = ws.at(b, W_V2, k);
             if (lane < d.nx + 2) {
-                double f = rd[lane] - mu * v1[lane] + v2[lane];
+                double f = sb[O_RD + lane] - mu * sb[O_V1 + lane] + sb[O_V2 + lane];
                 if (soc) {   // + Jc^T sigma (c_soc - (c - s))
                     const int a = d.st ? (lane < 4 ? lane : lane == 5 ? 4 : lane == 6 ? 5 : lane >= 8 ? lane - 2 : -1)
                                        : (lane == 0 ? 0 : lane == 2 ? 1 : lane == 3 ? 2 : lane >= 5 ? lane - 2 : -1);
@@ -616,37 +691,50 @@ __device__ bool riccati(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int lan
                 sm.g[gpos(d, lane)] = f;
             }
             if (lane >= d.nx && lane < n) sm.g[lane] = 0.0;   // lifted variables carry no linear term
+            if (k < H - 1) scatter_transition(sm, sb + O_AB, lane, d, stage_dims(N, k + 1));
         }
         __syncwarp();
-        if (lane == 0) {
-            const double* ob = ws.at(b, W_OBS, k);
-            const int si = d.st ? IS : QS, eyi = d.st ? IEY : QEY;
-            sm.G[si * 12 + si] += sf * ob[3];
-            sm.G[si * 12 + eyi] += sf * ob[4];
-            sm.G[eyi * 12 + si] += sf * ob[4];
-            sm.G[eyi * 12 + eyi] += sf * ob[5];
-            double p0, p1;
-            slew_weights(pr, dsb, k - 1, p0, p1);
-            const double cc[2] = {2.0 * sf * p0, 2.0 * sf * p1};
-            for (int j = 0; j < d.np; ++j) {
-                sm.G[(n + j) * 12 + n + j] += cc[j];
-                sm.G[(d.nx + j) * 12 + d.nx + j] += cc[j];
-                sm.G[(n + j) * 12 + d.nx + j] -= cc[j];
-                sm.G[(d.nx + j) * 12 + n + j] -= cc[j];
+        {   // closed-form Hessian parts: obstacle term (lane 0), control-continuity terms (lanes 1, 2), delta_w
+            const double* ob = sb + O_OBS;
+            if (lane == 0) {
+                const int si = d.st ? IS : QS, eyi = d.st ? IEY : QEY;
+                sm.G[si * 12 + si] += sf * ob[3];
+                sm.G[si * 12 + eyi] += sf * ob[4];
+                sm.G[eyi * 12 + si] += sf * ob[4];
+                sm.G[eyi * 12 + eyi] += sf * ob[5];
+            } else if (lane <= d.np) {
+                const int j = lane - 1;
+                const double cc = 2.0 * sf * ob[6 + j];
+                sm.G[(n + j) * 12 + n + j] += cc;
+                sm.G[(d.nx + j) * 12 + d.nx + j] += cc;
+                sm.G[(n + j) * 12 + d.nx + j] -= cc;
+                sm.G[(d.nx + j) * 12 + n + j] -= cc;
             }
-            for (int i = 0; i < d.nx; ++i) sm.G[i * 12 + i] += delta;
-            sm.G[n * 12 + n] += delta;
-            sm.G[(n + 1) * 12 + n + 1] += delta;
+            if (delta != 0.0) {
+                __syncwarp();
+                if (lane < d.nx) sm.G[lane * 12 + lane] += delta;
+                if (lane >= 30) sm.G[(n + lane - 30) * 12 + n + lane - 30] += delta;
+            }
         }
         __syncwarp();
         if (k < H - 1) {
             const Dims dn = stage_dims(N, k + 1);
-            build_transition(pr, ws, sm, b, lane, k, d, dn, a_gres);
-            for (int e = lane; e < dn.n * nn; e += 32) {      // PMm = P M
-                const int i = e / nn, j = e % nn;
-                double a = 0.0;
-                for (int l = 0; l < dn.n; ++l) a += sm.P[i * 10 + l] * sm.M[l * 12 + j];
-                sm.PMm[i * 12 + j] = a;
+            const int cnt = dn.n * nn;
+            {   // PMm = P M : up to 4 entries per lane, accumulated side by side
+                int ii[4], jj[4];
+                double acc[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    const int e = min(lane + 32 * t, cnt - 1);
+                    ii[t] = (e * rcp_nn) >> 16; jj[t] = e - ii[t] * nn;
+                }
+                for (int l = 0; l < dn.n; ++l) {
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) acc[t] += sm.P[ii[t] * 10 + l] * sm.M[l * 12 + jj[t]];
+                }
+#pragma unroll
+                for (int t = 0; t < 4; ++t)
+                    if (lane + 32 * t < cnt) sm.PMm[ii[t] * 12 + jj[t]] = acc[t];
             }
             if (lane < dn.n) {                                 // tv = P r + p
                 double a = sm.p[lane];
@@ -654,11 +742,22 @@ __device__ bool riccati(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int lan
                 sm.tv[lane] = a;
             }
             __syncwarp();
-            for (int e = lane; e < nn * nn; e += 32) {         // G += M^T (P M)
-                const int i = e / nn, j = e % nn;
-                double a = 0.0;
-                for (int l = 0; l < dn.n; ++l) a += sm.M[l * 12 + i] * sm.PMm[l * 12 + j];
-                sm.G[i * 12 + j] += a;
+            {   // G += M^T (P M)
+                const int cnt2 = nn * nn;
+                int ii[4], jj[4];
+                double acc[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    const int e = min(lane + 32 * t, cnt2 - 1);
+                    ii[t] = (e * rcp_nn) >> 16; jj[t] = e - ii[t] * nn;
+                }
+                for (int l = 0; l < dn.n; ++l) {
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) acc[t] += sm.M[l * 12 + ii[t]] * sm.PMm[l * 12 + jj[t]];
+                }
+#pragma unroll
+                for (int t = 0; t < 4; ++t)
+                    if (lane + 32 * t < cnt2) sm.G[ii[t] * 12 + jj[t]] += acc[t];
             }
             if (lane < nn) {                                   // g += M^T tv
                 double a = 0.0;
@@ -672,7 +771,8 @@ __device__ bool riccati(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int lan
                      rdd = sm.G[(n + 1) * 12 + n + 1];
         const double det = ra * rdd - rb * rb;
         if (!(ra > 0.0) || !(det > 0.0) || !isfinite(det)) { ok = false; break; }
-        const double i00 = rdd / det, i01 = -rb / det, i11 = ra / det;
+        const double idet = 1.0 / det;
+        const double i00 = rdd * idet, i01 = -rb * idet, i11 = ra * idet;
         double* km = ws.at(b, W_KM, k);
         if (lane < n) {
             const double g0 = sm.G[n * 12 + lane], g1 = sm.G[(n + 1) * 12 + lane];
@@ -686,11 +786,13 @@ __device__ bool riccati(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int lan
             sm.K[10] = f0; sm.K[22] = f1;
             km[20] = f0; km[21] = f1;
         }
+        // the equality residual of THIS stage's state is the offset of the transition into it (used at stage k-1)
+        if (lane < 12) sm.r[lane] = lane < d.nx ? -(soc ? ws.at(b, a_gres, k)[lane] : sb[O_GRES + lane]) : 0.0;
         __syncwarp();
         double* pm = ws.at(b, W_PM, k);
         double* pv = ws.at(b, W_PV, k);
         for (int e = lane; e < n * n; e += 32) {               // P = Gxx + Gxu K   (symmetrised)
-            const int i = e / n, j = e % n;
+            const int i = (e * rcp_n) >> 16, j = e - i * n;
             const double a = sm.G[i * 12 + j] + sm.G[i * 12 + n] * sm.K[j] + sm.G[i * 12 + n + 1] * sm.K[12 + j];
             const double c = sm.G[j * 12 + i] + sm.G[j * 12 + n] * sm.K[i] + sm.G[j * 12 + n + 1] * sm.K[12 + i];
             const double v = 0.5 * (a + c);
@@ -704,48 +806,63 @@ __device__ bool riccati(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int lan
         }
         __syncwarp();
     }
+    cp_async_wait<0>();
+    __syncwarp();
     if (!ok) return false;
-    // ---- forward substitution
-    if (lane < 12) sm.x[lane] = lane < 8 ? -ws.at(b, a_gres, 0)[lane] : 0.0;
+    // ---- forward substitution (stage blocks AB | GRES KM PV PM streamed two stages ahead)
+    for (int j = 0; j < FWD_DEPTH - 1; ++j) stage_fetch_fwd(ws, sm, b, j, H, lane);
+    stage_fetch_fwd(ws, sm, b, FWD_DEPTH - 1, H, lane);
+    cp_async_wait<FWD_DEPTH - 1>();
+    __syncwarp();
+    if (lane < 12) sm.x[lane] = lane < 8 ? -(soc ? ws.at(b, a_gres, 0)[lane] : sm.ring[F_GRES + lane]) : 0.0;
     __syncwarp();
     for (int k = 0; k < H; ++k) {
         const Dims d = stage_dims(N, k);
         const int n = d.n;
-        const double* km = ws.at(b, W_KM, k);
+        const double* fb = sm.ring + (k % FWD_DEPTH) * FWD_SLOT;
         if (lane < 2) {
+            const double* km = fb + F_KM;
             double a = km[20 + lane];
             for (int l = 0; l < n; ++l) a += km[lane * 10 + l] * sm.x[l];
             sm.x[n + lane] = a;
         }
+        if (k < H - 1) for (int e = lane; e < 120; e += 32) sm.M[e] = 0.0;
         __syncwarp();
         double* dy = ws.at(b, a_dy, k);
         if (lane < d.nx) {
             dy[lane] = sm.x[lane];
-            const double* pm = ws.at(b, W_PM, k);
-            double a = ws.at(b, W_PV, k)[lane];
+            const double* pm = fb + F_PM;
+            double a = fb[F_PV + lane];
             for (int l = 0; l < n; ++l) a += pm[lane * 10 + l] * sm.x[l];
             ws.at(b, a_dlam, k)[lane] = -a;
         }
         if (lane < 2) dy[d.nu_off + lane] = sm.x[n + lane];
         if (k < H - 1) {
             const Dims dn = stage_dims(N, k + 1);
-            build_transition(pr, ws, sm, b, lane, k, d, dn, a_gres);
+            scatter_transition(sm, fb + F_AB, lane, d, dn);
+            cp_async_wait<FWD_DEPTH - 2>();     // stage k+1's block (its GRES is the offset of this transition)
+            __syncwarp();
+            const double* fn = sm.ring + ((k + 1) % FWD_DEPTH) * FWD_SLOT;
             double a = 0.0;
             if (lane < dn.n) {
-                a = sm.r[lane];
+                a = lane < dn.nx ? -(soc ? ws.at(b, a_gres, k + 1)[lane] : fn[F_GRES + lane]) : 0.0;
                 for (int l = 0; l < n + 2; ++l) a += sm.M[lane * 12 + l] * sm.x[l];
             }
             __syncwarp();
             if (lane < dn.n) sm.x[lane] = a;
+            // slot of stage k is free now: stream stage k + FWD_DEPTH into it
+            stage_fetch_fwd(ws, sm, b, k + FWD_DEPTH, H, lane);
             __syncwarp();
         }
     }
+    cp_async_wait<0>();
+    __syncwarp();
     return true;
 }
 
 // slack / multiplier directions of a computed primal direction, fraction-to-the-boundary step sizes and the
 // directional derivative of the barrier objective (warp reductions)
-__device__ void slack_directions(const Prob& pr, const Ws& ws, int b, int lane, double mu, double tau, bool soc,
+__device__ __noinline__ void slack_directions(const Prob& pr, const Ws& ws, int b, int lane, double mu, double tau, bool soc,
                                  double& a_p, double& a_d, double& dphi) {
     const int H = pr.H, N = pr.N;
     a_p = 1.0; a_d = 1.0; dphi = 0.0;
@@ -771,7 +888,7 @@ __device__ void slack_directions(const Prob& pr, const Ws& ws, int b, int lane, 
 
 // evaluates the trial point (y + alpha dy, s + alpha ds) with lanes over stages; optionally keeps the constraint
 // values for a second-order correction.  Returns false on an evaluation error (NaN/Inf).
-__device__ bool trial_point(const Prob& pr, const Ws& ws, int b, int lane, double alpha, bool soc, bool store,
+__device__ __noinline__ bool trial_point(const Prob& pr, const Ws& ws, int b, int lane, double alpha, bool soc, bool store,
                             double& ft, double& tht, double& lnt) {
     const int H = pr.H, N = pr.N;
     ft = 0.0; tht = 0.0; lnt = 0.0;
@@ -799,7 +916,7 @@ __device__ bool trial_point(const Prob& pr, const Ws& ws, int b, int lane, doubl
 }
 
 // c_soc <- alpha * (first ? c(x_k) : c_soc) + c(trial)      for the equality rows and the (c - s) rows
-__device__ void soc_residual(const Prob& pr, const Ws& ws, int b, int lane, double alpha, bool /*soc*/, bool first) {
+__device__ __noinline__ void soc_residual(const Prob& pr, const Ws& ws, int b, int lane, double alpha, bool /*soc*/, bool first) {
     for (int k = lane; k < pr.H; k += 32) {
         const bool st = k < pr.N;
         double *gs = ws.at(b, W_GS, k), *cs = ws.at(b, W_CS, k);
@@ -814,7 +931,7 @@ __device__ void soc_residual(const Prob& pr, const Ws& ws, int b, int lane, doub
 // restoration substitute (oracle/nlp.py NLP.repair): guess-independent, dynamically feasible re-initialisation
 // -- hold the speed (Fx = drag), no steering rate, PointMass Fy follows the centre-line curvature -- with the
 // states re-generated by rolling the models out from x0
-__device__ void repair_rollout(const Prob& pr, const Ws& ws, int b, bool neutral = true) {
+__device__ __noinline__ void repair_rollout(const Prob& pr, const Ws& ws, int b, bool neutral = true) {
     const int H = pr.H, N = pr.N;
     const double* kap = pr.kappa + (size_t)b * H;
     const double* dsb = pr.ds + (size_t)b * H;
@@ -1048,7 +1165,7 @@ __device__ void step_instance(const Prob& pr, const Ws& ws, WarpSm& sm, int b, i
     }
 }
 
-__global__ void __launch_bounds__(32 * STEP_WARPS) k_step(Prob pr, Ws ws, int* next_list, int* next_count) {
+__global__ void __launch_bounds__(32 * STEP_WARPS, VC_STEP_MINBLOCKS) k_step(Prob pr, Ws ws, int* next_list, int* next_count) {
     __shared__ WarpSm s_all[STEP_WARPS];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int i = blockIdx.x * STEP_WARPS + wid;
@@ -1098,9 +1215,9 @@ static int fill_prob(vc_handle* h, Prob& pr, int B, const double* d_x0, const do
     pr.n_obs = (h->cfg.obstacles && d_obst) ? n_obs : 0;
     pr.z_init = getenv("VC_ZINIT") ? atof(getenv("VC_ZINIT")) : 0.0;
     pr.z_cap = getenv("VC_ZCAP") ? atof(getenv("VC_ZCAP")) : 0.0;
-    pr.stall_iters = getenv("VC_STALL") ? atoi(getenv("VC_STALL")) : 4;
+    pr.stall_iters = getenv("VC_STALL") ? atoi(getenv("VC_STALL")) : 1 << 30;   // barrier stall escape: off (superseded by the restoration)
     pr.max_soc = getenv("VC_MAXSOC") ? atoi(getenv("VC_MAXSOC")) : 4;
-    pr.restore_iters = getenv("VC_RESTORE") ? atoi(getenv("VC_RESTORE")) : 0;
+    pr.restore_iters = getenv("VC_RESTORE") ? atoi(getenv("VC_RESTORE")) : 4;
     pr.x0 = d_x0; pr.kappa = d_kappa; pr.ds = d_ds; pr.obst = d_obst;
     pr.X = pr.U = pr.obj = pr.kkt = nullptr; pr.status = pr.iters = nullptr;
     pr.act_list = pr.act_count = nullptr;
@@ -1218,8 +1335,16 @@ int debug_read(vc_handle* h, int b, int array, double* h_out, int n) {
     if (!h->d_ws) { set_error("debug_read: no workspace"); return -1; }
     const int H = h->cfg.N + h->cfg.M;
     Ws ws; ws.H = H; ws.stride = (size_t)WS_PER_STAGE * H + NSCAL; ws.base = (double*)h->d_ws;
-    const double* src = array < 0 ? ws.scal(b) : ws.arr(b, array);
     cudaStreamSynchronize(h->stream);
-    return check_cuda(cudaMemcpy(h_out, src, sizeof(double) * n, cudaMemcpyDeviceToHost), "debug_read");
+    if (array < 0) return check_cuda(cudaMemcpy(h_out, ws.scal(b), sizeof(double) * n, cudaMemcpyDeviceToHost), "debug_read");
+    if (array >= W_COUNT) { set_error("debug_read: bad array"); return -1; }
+    const int w = ws_width(array);   // returned as [H][width], gathered from the stage records
+    for (int k = 0; k < H && k * w < n; ++k) {
+        const int cnt = (n - k * w) < w ? (n - k * w) : w;
+        int rc = check_cuda(cudaMemcpy(h_out + (size_t)k * w, ws.rec(b, k) + ws_offset(array), sizeof(double) * cnt,
+                                       cudaMemcpyDeviceToHost), "debug_read");
+        if (rc) return rc;
+    }
+    return 0;
 }
 }  // namespace vc
