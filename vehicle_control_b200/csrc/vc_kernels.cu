@@ -211,7 +211,7 @@ __global__ void k_tyre_forces(Params p, int B, const double* __restrict__ x, con
     tyres(p, x[(size_t)b * 8 + IUX], x[(size_t)b * 8 + IUY], x[(size_t)b * 8 + IR], x[(size_t)b * 8 + IDELTA],
           u[(size_t)b * 2], ty);
     double* o = out + (size_t)b * 6;
-    o[0] = ty.fxf; o[1] = ty.fxr; o[2] = ty.fyf; o[3] = ty.fyr; o[4] = ty.alpha_f; o[5] = ty.alpha_r;
+    o[0] = ty.fxf; o[1] = ty.fxr; o[2] = ty.fyf; o[3] = ty.fyr; o[4] = atan(ty.tan_f); o[5] = atan(ty.tan_r);   // alpha_f, alpha_r (dynamic_car.py:111-115)
 }
 
 }  // namespace vc

@@ -22,8 +22,8 @@ template <class T> struct Tyres {
     T fxf, fxr;        // longitudinal force split          dynamic_car.py:78-86
     T fzf, fzr;        // normal loads                       :98-102
     T fymax_f, fymax_r;  // friction-ellipse lateral limit   :107-108
-    T alpha_f, alpha_r;  // slip angles                      :111-115
-    T tan_f, tan_r;
+    T tan_f, tan_r;    // tan of the slip angles             :111-115 (alpha itself is never needed, see tyres())
+    T sd, cd;          // sin / cos of the steering angle (shared with the chassis equations)
     T fyf, fyr;        // modified Fiala lateral forces      :121-142
 };
 
@@ -43,19 +43,25 @@ template <class T> VC_HD void normal_loads(const Params& p, const T& Ux, const T
     fzr = (p.a / p.l) * p.m * base + shift;
 }
 
-// modified Fiala brush model; branch chosen on values (CasADi if_else semantics)
+// modified Fiala brush model; branch chosen on values (CasADi if_else semantics).  The reference tests
+// |alpha| <= alpha_mod = atan(3 Fymax eps / C); tan is monotone on (-pi/2, pi/2), so the same branch is taken by
+// |tan alpha| <= 3 Fymax eps / C, and sign(alpha) = sign(tan alpha): no inverse trigonometry on the device.
 template <class T>
-VC_HD T fiala(double C, double eps, const T& alpha, const T& ta, const T& fymax) {
-    const double amod = atan(3.0 * val(fymax) * eps / C);
-    if (fabs(val(alpha)) <= amod) {
+VC_HD T fiala(double C, double eps, const T& ta, const T& fymax) {
+    const double tmod = 3.0 * val(fymax) * eps / C;
+    if (fabs(val(ta)) <= tmod) {
         const T inv = recip(fymax);
         return -C * ta + (C * C / 3.0) * (ad_abs(ta) * ta) * inv
                - (C * C * C / 27.0) * (ta * ta * ta) * (inv * inv);
     }
-    const double sg = val(alpha) > 0.0 ? 1.0 : (val(alpha) < 0.0 ? -1.0 : 0.0);
+    const double sg = val(ta) > 0.0 ? 1.0 : (val(ta) < 0.0 ? -1.0 : 0.0);
     return -C * (1 - 2 * eps + eps * eps) * ta - (3 * eps * eps - 2 * eps * eps * eps) * sg * fymax;
 }
 
+// Slip angles (dynamic_car.py:111-115): alpha_f = atan((Uy + a r)/Ux) - delta, alpha_r = atan((Uy - b r)/Ux).  Every use
+// of them downstream is through tan(alpha) (tyre force, slip cost) or cos(alpha) (friction-limit rows), so they are
+// carried as tangents: tan(alpha_r) = z_r, tan(alpha_f) = (z_f cos(delta) - sin(delta)) / (cos(delta) + z_f sin(delta))
+// -- the same functions of the state as the reference's atan/tan chain (to rounding), without fp64 atan/tan calls.
 template <class T>
 VC_HD void tyres(const Params& p, const T& Ux, const T& Uy, const T& r, const T& delta, const T& Fx,
                  Tyres<T>& o) {
@@ -66,13 +72,16 @@ VC_HD void tyres(const Params& p, const T& Ux, const T& Uy, const T& r, const T&
     o.fymax_f = ad_sqrt(lf * lf - qf * qf);
     o.fymax_r = ad_sqrt(lr * lr - qr * qr);
     const T iux = recip(Ux);
-    o.alpha_f = ad_atan((Uy + p.a * r) * iux) - delta;
-    o.alpha_r = ad_atan((Uy - p.b * r) * iux);
-    o.tan_f = ad_tan(o.alpha_f);
-    o.tan_r = ad_tan(o.alpha_r);
-    o.fyf = fiala(p.Caf, p.eps, o.alpha_f, o.tan_f, o.fymax_f);
-    o.fyr = fiala(p.Car, p.eps, o.alpha_r, o.tan_r, o.fymax_r);
+    const T zf = (Uy + p.a * r) * iux;
+    ad_sincos(delta, o.sd, o.cd);
+    o.tan_f = (zf * o.cd - o.sd) * recip(o.cd + zf * o.sd);
+    o.tan_r = (Uy - p.b * r) * iux;
+    o.fyf = fiala(p.Caf, p.eps, o.tan_f, o.fymax_f);
+    o.fyr = fiala(p.Car, p.eps, o.tan_r, o.fymax_r);
 }
+
+// cos(alpha) from tan(alpha), |alpha| < pi/2
+template <class T> VC_HD T cos_from_tan(const T& t) { return recip(ad_sqrt(1.0 + t * t)); }
 
 // SingleTrack right-hand side. SPATIAL=false: d/dt (dynamic_car.py:153-160); true: d/ds (:170-187).
 template <bool SPATIAL, class T>
@@ -81,8 +90,8 @@ VC_HD void st_rhs(const Params& p, const T* x, const T* u, double kappa, T* f) {
     const T &Fx = u[0], &w = u[1];
     Tyres<T> ty;
     tyres(p, Ux, Uy, r, delta, Fx, ty);
-    T sd, cd, se, ce;
-    ad_sincos(delta, sd, cd);
+    T se, ce;
+    const T &sd = ty.sd, &cd = ty.cd;
     ad_sincos(epsi, se, ce);
     const T Fd = p.Frr + p.Cd * (Ux * Ux);
     const T lat = ty.fyf * cd + ty.fxf * sd;

@@ -54,8 +54,8 @@ VC_HD void st_cost_ineq(const Params& p, const Cfg& c, const T* y, double ds, bo
         cost = cost + c.w_ey * sq(ey) + c.w_epsi * sq(epsi);
     }
     // ---- inequalities :91-128 (emission order)
-    const T bf = p.muf * ty.fzf * ad_cos(ty.alpha_f);
-    const T br = p.mur * ty.fzr * ad_cos(ty.alpha_r);
+    const T bf = p.muf * ty.fzf * cos_from_tan(ty.tan_f);
+    const T br = p.mur * ty.fzr * cos_from_tan(ty.tan_r);
     ineq[0] = Ux - relax_lo(c.Ux_min, rl);
     ineq[1] = delta - relax_lo(c.delta_min, rl);
     ineq[2] = relax_hi(c.delta_max, rl) - delta;

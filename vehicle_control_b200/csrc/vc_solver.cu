@@ -115,6 +115,8 @@ struct Prob {   // device-side view of one vc_nmpc_solve call
     int B, N, M, H, n_obs;
     int stall_iters;   // consecutive shortened steps before the barrier parameter is forced down
     int max_soc;       // second-order correction steps per iteration (IPOPT max_soc = 4)
+    int max_damp;      // damped re-solves of one iteration's direction before the iterate is restored / given up
+    int giveup_iters;  // consecutive shortened steps after the last restoration before the instance is given up
     int restore_iters; // > 0: consecutive shortened steps before the iterate is projected onto the dynamics (restoration)
     double z_cap;      // > 0: initial multipliers min(mu/s, z_cap)
     double z_init;   // > 0: constant initial inequality multipliers (IPOPT warm_start_mult_bound_push); else mu/s
@@ -1038,6 +1040,12 @@ __device__ void step_instance(const Prob& pr, const Ws& ws, WarpSm& sm, int b, i
         }
         return;
     }
+    // all restorations used and the steps are still being cut at an infeasible iterate: give the instance up (IPOPT ends
+    // such runs with "restoration failed"); it would otherwise crawl to max_iter and hold the whole batch's tail
+    if (pr.restore_iters > 0 && (int)sc[S_NREST] >= 3 && n_short >= pr.giveup_iters && m.theta > 1e-6) {
+        finalize(pr, ws, b, lane, VC_LINESEARCH_FAIL, obj, err0);
+        return;
+    }
     const double tau = fmax(IpmConst::tau_min, 1.0 - mu);
     const double theta = m.theta, phi = sf * m.f - mu * m.lns;
     double theta0 = sc[S_THETA0];
@@ -1049,6 +1057,7 @@ __device__ void step_instance(const Prob& pr, const Ws& ws, WarpSm& sm, int b, i
     int dbg_nan = 0;
     double dbg_tht2 = 0.0, dbg_ap2 = 0.0;
     bool accepted = false, failed = false;
+    int n_damp = 0;
     double* filt_t = sc + S_FILT;
     double* filt_p = sc + S_FILP;
     bool use_soc = false;
@@ -1121,7 +1130,7 @@ __device__ void step_instance(const Prob& pr, const Ws& ws, WarpSm& sm, int b, i
         if (accepted) break;
         // no acceptable step along this direction: damp it (larger delta_w) and retry; IPOPT would restore here
         trial = fmax(trial, 1e-4) * 100.0;
-        if (trial > 1e12) failed = true;
+        if (trial > 1e12 || ++n_damp > pr.max_damp) failed = true;
     }
     if (failed) {
         const int restarts = (int)sc[S_RESTARTS];
@@ -1216,6 +1225,8 @@ static int fill_prob(vc_handle* h, Prob& pr, int B, const double* d_x0, const do
     pr.z_init = getenv("VC_ZINIT") ? atof(getenv("VC_ZINIT")) : 0.0;
     pr.z_cap = getenv("VC_ZCAP") ? atof(getenv("VC_ZCAP")) : 0.0;
     pr.stall_iters = getenv("VC_STALL") ? atoi(getenv("VC_STALL")) : 1 << 30;   // barrier stall escape: off (superseded by the restoration)
+    pr.max_damp = getenv("VC_MAXDAMP") ? atoi(getenv("VC_MAXDAMP")) : 3;
+    pr.giveup_iters = getenv("VC_GIVEUP") ? atoi(getenv("VC_GIVEUP")) : 12;
     pr.max_soc = getenv("VC_MAXSOC") ? atoi(getenv("VC_MAXSOC")) : 4;
     pr.restore_iters = getenv("VC_RESTORE") ? atoi(getenv("VC_RESTORE")) : 4;
     pr.x0 = d_x0; pr.kappa = d_kappa; pr.ds = d_ds; pr.obst = d_obst;
