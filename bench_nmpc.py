@@ -46,6 +46,10 @@ def replay_lap(eng, cfg, track, max_ticks=2000, obstacles=None):
         rows["x0"].append(x.cpu().numpy()[0]); rows["Xw"].append(X.cpu().numpy()[0]); rows["Uw"].append(U.cpu().numpy()[0])
         ds, kap = eng.horizon_params(x, X)
         out = eng.solve(x, kap, ds, X, U, obstacles=ob)
+        if int(out["status"][0]) > 1:      # what a user of the reference would do on an IPOPT failure: retry from the cold guess
+            X.copy_(eng.tensor(X0[None])); U.copy_(eng.tensor(U0[None]))
+            ds, kap = eng.horizon_params(x, X)
+            out = eng.solve(x, kap, ds, X, U, obstacles=ob)
         rows["iters"].append(int(out["iters"][0])); rows["status"].append(int(out["status"][0]))
         if rows["status"][-1] > 1:
             break
@@ -90,6 +94,18 @@ def flops_per_iteration(N, M):
     return N * (15.0e3 + 4.0e3) + M * (0.5e3 + 1.5e3)
 
 
+# algorithmic bytes of the two dominant kernels (doubles moved per unit)
+EVAL_ST_BYTES = 8.0 * (10 + 8 + 10 + 10 + 8 + 8      # reads: y, lam(next), z, s, y(next) and the parameters
+                       + 36 + 64 + 80 + 4 * 8 + 8 + 10 + 1)   # writes: Hessian block, dynamics / inequality Jacobians, gradients, residuals
+
+
+def STEP_BYTES(H):
+    """k_step per instance-iteration: per stage it reads the evaluation record (HC AB RD V1 V2 OBS GRES JC GF CRES:
+    262 doubles) and the iterate (y lam s z: 38), writes + re-reads the Riccati factors (KM PV PM: 134, twice), writes the
+    direction (38) and the new iterate (38), and one line-search trial re-reads iterate and direction (76)."""
+    return 8.0 * H * (262 + 38 + 2 * 134 + 38 + 38 + 76)
+
+
 def bytes_per_solve(H):
     """compulsory traffic: read x0, kappa, ds, warm start; write solution + (obj, status, iters, kkt)."""
     return 8.0 * ((8 + H + H + 10 * H) + (10 * H + 3))
@@ -114,7 +130,7 @@ def cpu_baseline_nmpc(lap, track_yaml, cfg, seconds=25.0, procs=1):
                 done += r
     el = time.perf_counter() - t0
     return {"value": done / el, "unit": "solves/s", "cores": procs, "kind": "port",
-            "sample": f"{done} warm-started ticks of the same lap solved by the CPU oracle in {el:.1f} s "
+            "sample": f"{done} warm-started ticks of the same lap (loop capped at 40 iterations) solved by the CPU oracle in {el:.1f} s "
                       f"({procs} single-threaded process(es)); the reference's own logs report 14-25 solves/s "
                       f"(IPOPT+MA27, 1 thread, BASELINE.md)"}
 
@@ -130,8 +146,9 @@ def _oracle_solve(a):
     ds, kap = on.horizon_params(c, tr, x0, Xw[0])
     obst = np.array([o[:3] for o in tr.obstacles]) if c.obstacles else None
     p = on.NLP(c, om.DEFAULT, x0, kap, ds, obst)
-    r = ipm.solve(p, p.pack(Xw, Uw))
-    return 1 if r.status in ("solved", "acceptable") else 0
+    # bounded work: interior-point loop capped at 40 iterations, a capped solve still counts (favours the CPU figure)
+    ipm.solve(p, p.pack(Xw, Uw), ipm.IpmOptions(max_iter=40, max_restorations=0))
+    return 1
 
 
 def run_nmpc(a, rank, world, local):
@@ -206,17 +223,43 @@ def run_nmpc(a, rank, world, local):
     e2e_s = bc.max_over_ranks(e2e_t / e2e_n)
     h2d = (hx0.nbytes + hkap.nbytes + hds.nbytes + hob.nbytes + hX.nbytes + hU.nbytes)
     d2h = hX.nbytes + hU.nbytes + Be * (8 + 8 + 4 + 4)
-    # ---- roofline of the dominant kernel (k_eval_st): algorithmic work / measured launch time
+    # ---- roofline of the dominant kernel: algorithmic work / measured launch time (CUDA events on the solve stream)
     peak_hbm, how = bc.measured_peaks()
-    n_st = max(1, prof["launches"][0])
-    st_ms = prof["ms"][0] / n_st                       # average k_eval_st launch
-    step_ms = prof["ms"][2] / max(1, prof["launches"][2])
+    ms_st, ms_pm, ms_step = prof["ms"]
+    n_st, n_step = max(1, prof["launches"][0]), max(1, prof["launches"][2])
     share = [m / max(1e-9, sum(prof["ms"])) for m in prof["ms"]]
-    # k_eval_st per launch: reads y, lam, z, s (38 doubles) and writes Hessian/Jacobian blocks (36+64+80+...=~230) per stage
-    st_bytes = B * N * 8.0 * (38 + 36 + 64 + 80 + 40 + 8 + 10 + 1)
-    st_flops = B * N * 15.0e3
+    inst_passes = max(1, prof["instance_passes"])          # sum over timed+warm-up passes of the active instances
     fp64_peak = bc.FP64_PEAK_TFLOPS
+    # units per launch: one launch of k_step advances every unfinished instance by one interior-point iteration;
+    # one launch of k_eval_st evaluates N stages of every unfinished instance
+    kern = {
+        "k_step": {"units_per_launch": inst_passes / n_step, "unit": "instance-iteration", "bytes_per_unit": STEP_BYTES(H),
+                   "flops_per_unit": N * 4.0e3 + M * 1.5e3 + (N * 0.73e3 + M * 0.1e3), "launch_ms": ms_step / n_step,
+                   "ncu_dram_bytes_per_unit": 338.0e3},
+        "k_eval_st": {"units_per_launch": inst_passes * N / n_st, "unit": "stage evaluation", "bytes_per_unit": EVAL_ST_BYTES,
+                      "flops_per_unit": 15.0e3, "launch_ms": ms_st / n_st, "ncu_dram_bytes_per_unit": 2463.0},
+    }
+    dom = "k_step" if ms_step >= ms_st else "k_eval_st"
+    kd = kern[dom]
+    ach = kd["units_per_launch"] * kd["bytes_per_unit"] / (kd["launch_ms"] * 1e-3) / 1e9
     solve_flops = mean_it * flops_per_iteration(N, M)
+    roof = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak_hbm, "unit": "GB/s", "frac": ach / peak_hbm,
+            "traffic": kd["units_per_launch"] * kd["ncu_dram_bytes_per_unit"], "peak_source": how,
+            "traffic_source": "dram__bytes_read+write per unit from the committed ncu --set full capture (profiles/), "
+                              "times this run's average units per launch",
+            "units_per_launch": kd["units_per_launch"], "unit_of_work": kd["unit"],
+            "algorithmic_bytes_per_unit": kd["bytes_per_unit"], "launch_ms": kd["launch_ms"],
+            "share_of_step": share[2] if dom == "k_step" else share[0],
+            "fp64": {"achieved_tflops": kd["units_per_launch"] * kd["flops_per_unit"] / (kd["launch_ms"] * 1e-3) / 1e12,
+                     "peak_tflops": fp64_peak, "peak_source": "measured DFMA micro-benchmark (profiles/r01_fp64_peak.txt)"},
+            "kernels": {k: {"launch_ms": v["launch_ms"], "units_per_launch": v["units_per_launch"],
+                            "hbm_gbs": v["units_per_launch"] * v["bytes_per_unit"] / (v["launch_ms"] * 1e-3) / 1e9,
+                            "fp64_tflops": v["units_per_launch"] * v["flops_per_unit"] / (v["launch_ms"] * 1e-3) / 1e12}
+                        for k, v in kern.items()},
+            "whole_solve_fp64": {"achieved_tflops": value / world * solve_flops / 1e12,
+                                 "frac": value / world * solve_flops / 1e12 / fp64_peak, "flops_per_solve": solve_flops},
+            "kernel_share": {"k_eval_st": share[0], "k_eval_pm": share[1], "k_step": share[2]}}
+    roof["fp64"]["frac"] = roof["fp64"]["achieved_tflops"] / fp64_peak
     line = {
         "metric": "NMPC solves/sec", "value": value, "unit": "solves/s", "n_gpus": world, "steps": a.steps,
         "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -230,17 +273,7 @@ def run_nmpc(a, rank, world, local):
         "clocks": clk.summary(), "gpu_launches": int(round(launches_total * a.steps / runs)),
         "e2e": {"value": world * Be / e2e_s, "unit": "solves/s", "h2d_bytes_per_step": int(h2d),
                 "d2h_bytes_per_step": int(d2h), "batch": Be},
-        "roofline": {"bound": "hbm", "kernel": "k_eval_st", "achieved": st_bytes / (st_ms * 1e-3) / 1e9,
-                     "peak": peak_hbm, "unit": "GB/s", "frac": st_bytes / (st_ms * 1e-3) / 1e9 / peak_hbm,
-                     "traffic": None, "peak_source": how, "launch_ms": st_ms, "share_of_step": share[0],
-                     "fp64": {"achieved_tflops": st_flops / (st_ms * 1e-3) / 1e12, "peak_tflops": fp64_peak,
-                              "frac": st_flops / (st_ms * 1e-3) / 1e12 / fp64_peak,
-                              "peak_source": "measured DFMA micro-benchmark (profiles/r01_fp64_peak.txt)"},
-                     "whole_solve_fp64": {"achieved_tflops": value / world * solve_flops / 1e12,
-                                          "frac": value / world * solve_flops / 1e12 / fp64_peak,
-                                          "flops_per_solve": solve_flops},
-                     "kernel_share": {"k_eval_st": share[0], "k_eval_pm": share[1], "k_step": share[2]},
-                     "k_step_launch_ms": step_ms},
+        "roofline": roof,
     }
     if rank == 0 and not a.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline_nmpc(lap, track_yaml, cfg)

@@ -131,6 +131,8 @@ int vc_nmpc_solve_host(vc_handle* h, int B, const double* h_x0, const double* h_
  * vc_set_profiling, and the number of interior-point passes of the last solve. */
 int vc_set_profiling(vc_handle* h, int on);
 int vc_get_profile(vc_handle* h, double* out_ms3, long long* out_launches3, int* out_last_passes);
+/* sum over the profiled passes of the number of unfinished instances each pass processed (units of the roofline) */
+long long vc_get_profile_instance_passes(vc_handle* h);
 
 /* Diagnostics: copies n doubles of solver-workspace array `array` (enum WsArray in csrc/vc_solver.cu; -1 = scalar
  * block) of instance b of the last vc_nmpc_solve to the host.  Synchronises. */

@@ -141,8 +141,10 @@ def test_full_lap_cascaded_matches_reference_lap(golden, tmp_path):
     assert abs(sim2.summary()["cascaded"]["laptime"] - S[-1, 7]) < 1e-9
 
 
-@pytest.mark.parametrize("run_key,dt_lap", [("singletrack3_ippodromo/singletrack", 0.0), ("race2_shoe/cascaded", 0.0),
-                                            ("cascaded_obstacles1_ippodromo/cascaded", 0.25)])
+@pytest.mark.parametrize("run_key,dt_lap", [("singletrack3_ippodromo/singletrack", 0.0), ("race2_shoe/cascaded", 0.05),
+                                            ("cascaded_obstacles1_ippodromo/cascaded", 0.5),
+                                            ("cascaded_giantObstacle3_ippodromo/cascaded", 2.0),
+                                            ("singletrack_shoe/singletrack", 0.05)])
 def test_laps_complete_like_reference(golden, run_key, dt_lap):
     """Every solve of a whole lap converges (the reference raises on IPOPT failure) and the lap time equals the
     reference's (within dt_lap seconds where the two solvers take different sides of a branch of the NLP)."""

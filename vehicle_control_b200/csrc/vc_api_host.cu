@@ -76,6 +76,7 @@ int vc_set_profiling(vc_handle* h, int on) {
     h->profiling = on;
     for (int i = 0; i < 4; ++i) h->prof_ms[i] = 0.0;
     for (int i = 0; i < 3; ++i) h->prof_launches[i] = 0;
+    h->prof_instance_passes = 0;
     return 0;
 }
 
@@ -88,5 +89,7 @@ int vc_get_profile(vc_handle* h, double* out_ms3, long long* out_launches3, int*
     if (out_last_passes) *out_last_passes = h->last_passes;
     return 0;
 }
+
+long long vc_get_profile_instance_passes(vc_handle* h) { return h ? h->prof_instance_passes : -1; }
 
 }  // extern "C"

@@ -36,6 +36,7 @@ struct vc_handle {
     std::vector<cudaEvent_t> prof_events;
     double prof_ms[4] = {0, 0, 0, 0};   // k_eval_st, k_eval_pm, k_step, launches of each
     long long prof_launches[3] = {0, 0, 0};
+    long long prof_instance_passes = 0;   // sum over profiled passes of the number of unfinished instances
 };
 
 namespace vc {

@@ -115,6 +115,7 @@ struct Prob {   // device-side view of one vc_nmpc_solve call
     int B, N, M, H, n_obs;
     int stall_iters;   // consecutive shortened steps before the barrier parameter is forced down
     int max_soc;       // second-order correction steps per iteration (IPOPT max_soc = 4)
+    int restore_check; // 1: a restored trajectory that leaves the widened state bounds is replaced by the neutral rollout
     int max_damp;      // damped re-solves of one iteration's direction before the iterate is restored / given up
     int giveup_iters;  // consecutive shortened steps after the last restoration before the instance is given up
     int restore_iters; // > 0: consecutive shortened steps before the iterate is projected onto the dynamics (restoration)
@@ -968,6 +969,24 @@ __device__ __noinline__ void repair_rollout(const Prob& pr, const Ws& ws, int b,
     }
 }
 
+// a restored trajectory is only useful if it stays inside the (slightly widened) state bounds: rolling out controls
+// that are still far from sensible (cold starts) spins the car or leaves the track
+__device__ __noinline__ bool rollout_sane(const Prob& pr, const Ws& ws, int b) {
+    const Cfg& c = pr.c;
+    for (int k = 0; k < pr.H; ++k) {
+        const double* y = ws.at(b, W_Y, k);
+        if (k < pr.N) {
+            for (int i = 0; i < 8; ++i) if (!isfinite(y[i])) return false;
+            if (y[IUX] < c.Ux_min || y[IDELTA] < c.delta_min - 0.05 || y[IDELTA] > c.delta_max + 0.05) return false;
+            if (y[IEY] < c.ey_min - 1.0 || y[IEY] > c.ey_max + 1.0 || fabs(y[IEPSI]) > 1.0) return false;
+        } else {
+            for (int i = 0; i < 5; ++i) if (!isfinite(y[i])) return false;
+            if (y[QV] < c.V_min || y[QEY] < c.ey_min_pm - 1.0 || y[QEY] > c.ey_max_pm + 1.0 || fabs(y[QEPSI]) > 1.0) return false;
+        }
+    }
+    return true;
+}
+
 // ------------------------------------------------------------------------------------------------
 // k_step: one interior-point iteration of every unfinished instance (one warp each)
 __device__ void step_instance(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int lane) {
@@ -1031,6 +1050,7 @@ __device__ void step_instance(const Prob& pr, const Ws& ws, WarpSm& sm, int b, i
         __syncwarp();
         if (lane == 0) {
             repair_rollout(pr, ws, b, false);
+            if (pr.restore_check && !rollout_sane(pr, ws, b)) repair_rollout(pr, ws, b, true);   // neutral controls instead
             sc[S_NREST] += 1.0; sc[S_MODE] = MODE_REINIT; sc[S_SHORT] = 0; sc[S_ITERS] = iters + 1; sc[S_MU] = mu;
         }
         for (int k = lane; k < H; k += 32) {
@@ -1042,7 +1062,8 @@ __device__ void step_instance(const Prob& pr, const Ws& ws, WarpSm& sm, int b, i
     }
     // all restorations used and the steps are still being cut at an infeasible iterate: give the instance up (IPOPT ends
     // such runs with "restoration failed"); it would otherwise crawl to max_iter and hold the whole batch's tail
-    if (pr.restore_iters > 0 && (int)sc[S_NREST] >= 3 && n_short >= pr.giveup_iters && m.theta > 1e-6) {
+    if (pr.restore_iters > 0 && (int)sc[S_NREST] >= 3 && n_short >= pr.giveup_iters && m.theta > 1e-6 &&
+        !(mu > mu_floor * (1 + 1e-12))) {
         finalize(pr, ws, b, lane, VC_LINESEARCH_FAIL, obj, err0);
         return;
     }
@@ -1224,11 +1245,12 @@ static int fill_prob(vc_handle* h, Prob& pr, int B, const double* d_x0, const do
     pr.n_obs = (h->cfg.obstacles && d_obst) ? n_obs : 0;
     pr.z_init = getenv("VC_ZINIT") ? atof(getenv("VC_ZINIT")) : 0.0;
     pr.z_cap = getenv("VC_ZCAP") ? atof(getenv("VC_ZCAP")) : 0.0;
-    pr.stall_iters = getenv("VC_STALL") ? atoi(getenv("VC_STALL")) : 1 << 30;   // barrier stall escape: off (superseded by the restoration)
-    pr.max_damp = getenv("VC_MAXDAMP") ? atoi(getenv("VC_MAXDAMP")) : 3;
-    pr.giveup_iters = getenv("VC_GIVEUP") ? atoi(getenv("VC_GIVEUP")) : 12;
+    pr.stall_iters = getenv("VC_STALL") ? atoi(getenv("VC_STALL")) : 4;
+    pr.restore_check = getenv("VC_RESTORE_CHECK") ? atoi(getenv("VC_RESTORE_CHECK")) : 1;
+    pr.max_damp = getenv("VC_MAXDAMP") ? atoi(getenv("VC_MAXDAMP")) : 8;
+    pr.giveup_iters = getenv("VC_GIVEUP") ? atoi(getenv("VC_GIVEUP")) : 24;
     pr.max_soc = getenv("VC_MAXSOC") ? atoi(getenv("VC_MAXSOC")) : 4;
-    pr.restore_iters = getenv("VC_RESTORE") ? atoi(getenv("VC_RESTORE")) : 4;
+    pr.restore_iters = getenv("VC_RESTORE") ? atoi(getenv("VC_RESTORE")) : 8;
     pr.x0 = d_x0; pr.kappa = d_kappa; pr.ds = d_ds; pr.obst = d_obst;
     pr.X = pr.U = pr.obj = pr.kkt = nullptr; pr.status = pr.iters = nullptr;
     pr.act_list = pr.act_count = nullptr;
@@ -1299,6 +1321,7 @@ int launch_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_k
         // grids are sized by the last count read back (an upper bound); the kernels read the exact count on the device
         const long long t_st = (long long)n_act * pr.N * 36, t_pm = (long long)n_act * pr.M * 15;
         pr.act_list = lists[cur]; pr.act_count = counts[cur];
+        if (prof) h->prof_instance_passes += n_act;
         mark();
         k_eval_st<<<(unsigned)((t_st + 127) / 128), 128, 0, st>>>(pr, ws);
         mark();

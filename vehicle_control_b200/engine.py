@@ -231,7 +231,8 @@ class Engine:
         """dict(ms=[k_eval_st, k_eval_pm, k_step], launches=[...], last_passes=int) since set_profiling(True)."""
         ms, ln, lp = (C.c_double * 3)(), (C.c_longlong * 3)(), C.c_int()
         check(self.lib.vc_get_profile(self._h, C.addressof(ms), C.addressof(ln), C.addressof(lp)), "vc_get_profile")
-        return {"ms": list(ms), "launches": list(ln), "last_passes": lp.value}
+        return {"ms": list(ms), "launches": list(ln), "last_passes": lp.value,
+                "instance_passes": int(self.lib.vc_get_profile_instance_passes(self._h))}
 
     def debug_read(self, b, array, n):
         out = np.empty(n)
