@@ -114,11 +114,12 @@ def test_c5_rollout_composition_and_linearisation(golden):
     X, AB = eng.rollout_st(x0, U, kap, ds, jac=True)
     assert bool(torch.isfinite(X).all()) and bool(torch.isfinite(AB).all())
     Xs = eng.rollout_st(x0, U, kap, ds)
-    assert torch.equal(X, Xs)                                  # the Jacobian kernel carries the same states
-    h = N // 2                                                 # N steps = h steps followed by N-h steps
+    # the Jacobian kernel carries the same states (dual-number and plain arithmetic contract FMAs differently)
+    assert ((X - Xs).abs() / Xs.abs().clamp(min=1.0)).max().item() < 1e-12
+    h = N // 2                                                 # N steps = h steps followed by N-h steps, bit for bit
     Xa = eng.rollout_st(x0, U[:, :h].contiguous(), kap[:, :h].contiguous(), ds[:, :h].contiguous())
     Xb = eng.rollout_st(Xa[:, -1].contiguous(), U[:, h:].contiguous(), kap[:, h:].contiguous(), ds[:, h:].contiguous())
-    assert torch.equal(Xa, X[:, :h + 1]) and torch.equal(Xb, X[:, h:])
+    assert torch.equal(Xa, Xs[:, :h + 1]) and torch.equal(Xb, Xs[:, h:])
     # first-order prediction of a perturbed first step by [A|B] (directional finite difference)
     rng = np.random.default_rng(3)
     dx = torch.as_tensor(rng.normal(0, 1, (B, 8)), device=X.device) * 1e-6
