@@ -130,7 +130,7 @@ def cpu_baseline_nmpc(lap, track_yaml, cfg, seconds=25.0, procs=1):
                 done += r
     el = time.perf_counter() - t0
     return {"value": done / el, "unit": "solves/s", "cores": procs, "kind": "port",
-            "sample": f"{done} warm-started ticks of the same lap (loop capped at 40 iterations) solved by the CPU oracle in {el:.1f} s "
+            "sample": f"{done} warm-started ticks of the same lap (loop capped at 30 iterations) solved by the CPU oracle in {el:.1f} s "
                       f"({procs} single-threaded process(es)); the reference's own logs report 14-25 solves/s "
                       f"(IPOPT+MA27, 1 thread, BASELINE.md)"}
 
@@ -146,8 +146,8 @@ def _oracle_solve(a):
     ds, kap = on.horizon_params(c, tr, x0, Xw[0])
     obst = np.array([o[:3] for o in tr.obstacles]) if c.obstacles else None
     p = on.NLP(c, om.DEFAULT, x0, kap, ds, obst)
-    # bounded work: interior-point loop capped at 40 iterations, a capped solve still counts (favours the CPU figure)
-    ipm.solve(p, p.pack(Xw, Uw), ipm.IpmOptions(max_iter=40, max_restorations=0))
+    # bounded work: interior-point loop capped at 30 iterations, a capped solve still counts (favours the CPU figure)
+    ipm.solve(p, p.pack(Xw, Uw), ipm.IpmOptions(max_iter=30, max_restorations=0))
     return 1
 
 

@@ -25,9 +25,9 @@ def _solve_tick(args):
     cfg, x0, kap, ds, obst, X0, U0 = args
     c = on.MpcCfg.from_config(cfg)
     p = on.NLP(c, om.DEFAULT, x0, kap, ds, obst if c.obstacles else None)
-    # bounded work per step: the interior-point loop is capped at 40 iterations (the B200 arm's median is 17, its
+    # bounded work per step: the interior-point loop is capped at 30 iterations (the B200 arm's median is 17, its
     # p90 37); a capped solve still counts as one solve, which can only favour this CPU arm
-    r = ipm.solve(p, p.pack(X0, U0), ipm.IpmOptions(max_iter=40, max_restorations=0))
+    r = ipm.solve(p, p.pack(X0, U0), ipm.IpmOptions(max_iter=30, max_restorations=0))
     return 1
 
 
@@ -78,6 +78,9 @@ def run_reference(a, workload):
     cores = max(1, len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1))
     procs = min(cores, 64)
     steps, warm = max(1, a.steps), max(0, a.warmup)
+    # one single-threaded worker per core: keep BLAS / OpenMP from oversubscribing the cores (inherited by the workers)
+    for v in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS", "NUMEXPR_NUM_THREADS"):
+        os.environ[v] = "1"
     ctx = mp.get_context("spawn")
     with ctx.Pool(procs) as pool:
         if workload == "rollout":
@@ -93,7 +96,7 @@ def run_reference(a, workload):
             cfg, tasks = _nmpc_tasks(procs)
             fn, unit, metric = _solve_tick, "solves/s", "NMPC solves/sec"
             wl = "C3: cascaded NMPC 20+35 with obstacles, ippodromo, warm-started perturbed instances"
-            sample = (f"{procs} warm-started perturbed instances per step (one per worker, interior-point loop capped at 40 "
+            sample = (f"{procs} warm-started perturbed instances per step (one per worker, interior-point loop capped at 30 "
                       f"iterations and counted as solved), oracle/nlp.py + oracle/ipm.py; "
                       f"the reference's own logs report 14-25 solves/s for IPOPT+MA27 on 1 thread (BASELINE.md)")
         for _ in range(min(warm, 1)):       # one warm-up pass is enough to page the workers in (each pass is ~30 s)

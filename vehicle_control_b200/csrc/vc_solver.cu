@@ -644,6 +644,120 @@ __device__ __forceinline__ void scatter_transition(WarpSm& sm, const double* ab,
         sm.M[(dn.nx + 1) * 12 + gpos(d, c_act_st[lane - 8])] = ab[5 * 8 + lane - 8];
 }
 
+// ---- stage products of the backward sweep: PMm = P M, tv = P r + p, G += M^T PMm, g += M^T tv
+// generic shapes: four interleaved accumulators per lane, entry indices by reciprocal multiplication
+__device__ __noinline__ void stage_products_generic(WarpSm& sm, int lane, int dnn, int nn, int rcp_nn) {
+    const int cnt = dnn * nn;
+            {   // PMm = P M : up to 4 entries per lane, accumulated side by side
+                int ii[4], jj[4];
+                double acc[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    const int e = min(lane + 32 * t, cnt - 1);
+                    ii[t] = (e * rcp_nn) >> 16; jj[t] = e - ii[t] * nn;
+                }
+                for (int l = 0; l < dnn; ++l) {
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) acc[t] += sm.P[ii[t] * 10 + l] * sm.M[l * 12 + jj[t]];
+                }
+#pragma unroll
+                for (int t = 0; t < 4; ++t)
+                    if (lane + 32 * t < cnt) sm.PMm[ii[t] * 12 + jj[t]] = acc[t];
+            }
+            if (lane < dnn) {                                 // tv = P r + p
+                double a = sm.p[lane];
+                for (int l = 0; l < dnn; ++l) a += sm.P[lane * 10 + l] * sm.r[l];
+                sm.tv[lane] = a;
+            }
+            __syncwarp();
+            {   // G += M^T (P M)
+                const int cnt2 = nn * nn;
+                int ii[4], jj[4];
+                double acc[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    const int e = min(lane + 32 * t, cnt2 - 1);
+                    ii[t] = (e * rcp_nn) >> 16; jj[t] = e - ii[t] * nn;
+                }
+                for (int l = 0; l < dnn; ++l) {
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) acc[t] += sm.M[l * 12 + ii[t]] * sm.PMm[l * 12 + jj[t]];
+                }
+#pragma unroll
+                for (int t = 0; t < 4; ++t)
+                    if (lane + 32 * t < cnt2) sm.G[ii[t] * 12 + jj[t]] += acc[t];
+            }
+            if (lane < nn) {                                   // g += M^T tv
+                double a = 0.0;
+                for (int l = 0; l < dnn; ++l) a += sm.M[l * 12 + lane] * sm.tv[l];
+                sm.g[lane] += a;
+            }
+            __syncwarp();
+}
+
+// compile-time shapes: every lane owns a 2x2 block of the result (one shared-memory load per multiply-add instead of
+// two, 16-byte loads along the rows); G is symmetric, so only its upper block triangle is computed and mirrored
+template <int DN, int NN>
+__device__ __forceinline__ void stage_products(WarpSm& sm, int lane) {
+    constexpr int RB = (DN + 1) / 2, CB = (NN + 1) / 2;
+    static_assert(RB * CB <= 32 && CB * (CB + 1) / 2 <= 32, "one block per lane");
+    if (lane < RB * CB) {
+        const int bi = lane / CB, bj = lane - bi * CB, i0 = 2 * bi, j0 = 2 * bj;
+        double a00 = 0.0, a01 = 0.0, a10 = 0.0, a11 = 0.0;
+#pragma unroll
+        for (int l = 0; l < DN; ++l) {
+            const double p0 = sm.P[i0 * 10 + l], p1 = sm.P[(i0 + 1) * 10 + l];
+            const double2 m = *reinterpret_cast<const double2*>(&sm.M[l * 12 + j0]);
+            a00 += p0 * m.x; a01 += p0 * m.y; a10 += p1 * m.x; a11 += p1 * m.y;
+        }
+        sm.PMm[i0 * 12 + j0] = a00;
+        if (j0 + 1 < NN) sm.PMm[i0 * 12 + j0 + 1] = a01;
+        if (i0 + 1 < DN) {
+            sm.PMm[(i0 + 1) * 12 + j0] = a10;
+            if (j0 + 1 < NN) sm.PMm[(i0 + 1) * 12 + j0 + 1] = a11;
+        }
+    }
+    if (lane < DN) {                                       // tv = P r + p
+        double a = sm.p[lane];
+#pragma unroll
+        for (int l = 0; l < DN; ++l) a += sm.P[lane * 10 + l] * sm.r[l];
+        sm.tv[lane] = a;
+    }
+    __syncwarp();
+    if (lane < CB * (CB + 1) / 2) {                        // upper block triangle of G += M^T (P M)
+        int bj = (int)((sqrtf(8.0f * lane + 1.0f) - 1.0f) * 0.5f);
+        if ((bj + 1) * (bj + 2) / 2 <= lane) ++bj;
+        if (bj * (bj + 1) / 2 > lane) --bj;
+        const int bi = lane - bj * (bj + 1) / 2;           // bi <= bj
+        const int i0 = 2 * bi, j0 = 2 * bj;
+        double a00 = 0.0, a01 = 0.0, a10 = 0.0, a11 = 0.0;
+#pragma unroll
+        for (int l = 0; l < DN; ++l) {
+            const double2 mi = *reinterpret_cast<const double2*>(&sm.M[l * 12 + i0]);
+            const double2 q = *reinterpret_cast<const double2*>(&sm.PMm[l * 12 + j0]);
+            a00 += mi.x * q.x; a01 += mi.x * q.y; a10 += mi.y * q.x; a11 += mi.y * q.y;
+        }
+        const bool i1 = i0 + 1 < NN, j1 = j0 + 1 < NN;
+        sm.G[i0 * 12 + j0] += a00;
+        if (j1) sm.G[i0 * 12 + j0 + 1] += a01;
+        if (i1) sm.G[(i0 + 1) * 12 + j0] += a10;
+        if (i1 && j1) sm.G[(i0 + 1) * 12 + j0 + 1] += a11;
+        if (bi != bj) {                                    // mirror block
+            sm.G[j0 * 12 + i0] += a00;
+            if (j1) sm.G[(j0 + 1) * 12 + i0] += a01;
+            if (i1) sm.G[j0 * 12 + i0 + 1] += a10;
+            if (i1 && j1) sm.G[(j0 + 1) * 12 + i0 + 1] += a11;
+        }
+    } else if (lane >= 32 - NN) {                          // g += M^T tv on the idle lanes
+        const int c = lane - (32 - NN);
+        double a = 0.0;
+#pragma unroll
+        for (int l = 0; l < DN; ++l) a += sm.M[l * 12 + c] * sm.tv[l];
+        sm.g[c] += a;
+    }
+    __syncwarp();
+}
+
 // Backward Riccati sweep + forward substitution of the condensed KKT system
 //   [Hc + delta I  Jg^T] [dw  ]   [-(rd - mu v1 + v2)]
 //   [Jg            0   ] [dlam] = [-g                ]
@@ -722,52 +836,12 @@ __device__ __noinline__ bool riccati(const Prob& pr, const Ws& ws, WarpSm& sm, i
         __syncwarp();
         if (k < H - 1) {
             const Dims dn = stage_dims(N, k + 1);
-            const int cnt = dn.n * nn;
-            {   // PMm = P M : up to 4 entries per lane, accumulated side by side
-                int ii[4], jj[4];
-                double acc[4] = {0.0, 0.0, 0.0, 0.0};
-#pragma unroll
-                for (int t = 0; t < 4; ++t) {
-                    const int e = min(lane + 32 * t, cnt - 1);
-                    ii[t] = (e * rcp_nn) >> 16; jj[t] = e - ii[t] * nn;
-                }
-                for (int l = 0; l < dn.n; ++l) {
-#pragma unroll
-                    for (int t = 0; t < 4; ++t) acc[t] += sm.P[ii[t] * 10 + l] * sm.M[l * 12 + jj[t]];
-                }
-#pragma unroll
-                for (int t = 0; t < 4; ++t)
-                    if (lane + 32 * t < cnt) sm.PMm[ii[t] * 12 + jj[t]] = acc[t];
-            }
-            if (lane < dn.n) {                                 // tv = P r + p
-                double a = sm.p[lane];
-                for (int l = 0; l < dn.n; ++l) a += sm.P[lane * 10 + l] * sm.r[l];
-                sm.tv[lane] = a;
-            }
-            __syncwarp();
-            {   // G += M^T (P M)
-                const int cnt2 = nn * nn;
-                int ii[4], jj[4];
-                double acc[4] = {0.0, 0.0, 0.0, 0.0};
-#pragma unroll
-                for (int t = 0; t < 4; ++t) {
-                    const int e = min(lane + 32 * t, cnt2 - 1);
-                    ii[t] = (e * rcp_nn) >> 16; jj[t] = e - ii[t] * nn;
-                }
-                for (int l = 0; l < dn.n; ++l) {
-#pragma unroll
-                    for (int t = 0; t < 4; ++t) acc[t] += sm.M[l * 12 + ii[t]] * sm.PMm[l * 12 + jj[t]];
-                }
-#pragma unroll
-                for (int t = 0; t < 4; ++t)
-                    if (lane + 32 * t < cnt2) sm.G[ii[t] * 12 + jj[t]] += acc[t];
-            }
-            if (lane < nn) {                                   // g += M^T tv
-                double a = 0.0;
-                for (int l = 0; l < dn.n; ++l) a += sm.M[l * 12 + lane] * sm.tv[l];
-                sm.g[lane] += a;
-            }
-            __syncwarp();
+            // G += M^T P M, g += M^T (P r + p): register-blocked for the stage shapes of the shipped controllers
+            if (dn.n == 9 && nn == 11) stage_products<9, 11>(sm, lane);
+            else if (dn.n == 7 && nn == 9) stage_products<7, 9>(sm, lane);
+            else if (dn.n == 7 && nn == 11) stage_products<7, 11>(sm, lane);
+            else if (dn.n == 9 && nn == 10) stage_products<9, 10>(sm, lane);
+            else stage_products_generic(sm, lane, dn.n, nn, rcp_nn);
         }
         // reduced Hessian of the two controls
         const double ra = sm.G[n * 12 + n], rb = 0.5 * (sm.G[n * 12 + n + 1] + sm.G[(n + 1) * 12 + n]),
