@@ -87,6 +87,11 @@ constexpr int WS_FWD1 = ws_offset(W_Y);
 static_assert(WS_PER_STAGE % 2 == 0 && WS_BWD % 2 == 0 && WS_FWD0 % 2 == 0 && WS_FWD1 % 2 == 0 &&
               ws_offset(W_AB) % 2 == 0 && ws_offset(W_RD) % 2 == 0, "16-byte alignment of the staged blocks");
 static_assert(W_COUNT == 31, "update make_ws_table / c_ws_off");
+constexpr int O_IT = ws_offset(W_Y), O_DIR = ws_offset(W_DY), O_DIR2 = ws_offset(W_DY2);
+static_assert(ws_offset(W_LAM) == O_IT + 10 && ws_offset(W_S) == O_IT + 18 && ws_offset(W_Z) == O_IT + 28 &&
+              ws_offset(W_DLAM) == O_DIR + 10 && ws_offset(W_DSL) == O_DIR + 18 && ws_offset(W_DZ) == O_DIR + 28 &&
+              ws_offset(W_DLAM2) == O_DIR2 + 10 && ws_offset(W_DSL2) == O_DIR2 + 18 && ws_offset(W_DZ2) == O_DIR2 + 28,
+              "iterate / direction blocks must share one layout");
 constexpr int NSCAL = 64;
 // scalar block of an instance
 enum Scal { S_MU = 0, S_SF, S_DELTA_LAST, S_THETA0, S_NFILT, S_ACC, S_MODE, S_RESTARTS, S_OBJ, S_ERR, S_ITERS,
@@ -941,24 +946,41 @@ __device__ __noinline__ bool riccati(const Prob& pr, const Ws& ws, WarpSm& sm, i
 // directional derivative of the barrier objective (warp reductions)
 __device__ __noinline__ void slack_directions(const Prob& pr, const Ws& ws, int b, int lane, double mu, double tau, bool soc,
                                  double& a_p, double& a_d, double& dphi) {
-    const int H = pr.H, N = pr.N;
+    const int H = pr.H, N = pr.N, M = pr.M;
     a_p = 1.0; a_d = 1.0; dphi = 0.0;
-    for (int k = lane; k < H; k += 32) {
-        const bool st = k < N;
-        const int na = st ? 8 : 5;
-        const double *jc = ws.at(b, W_JC, k), *dy = ws.at(b, soc ? W_DY2 : W_DY, k), *cr = ws.at(b, W_CRES, k);
-        const double *s = ws.at(b, W_S, k), *z = ws.at(b, W_Z, k), *gf = ws.at(b, W_GF, k), *cs = ws.at(b, W_CS, k);
-        double *dsl = ws.at(b, soc ? W_DSL2 : W_DSL, k), *dz = ws.at(b, soc ? W_DZ2 : W_DZ, k);
-        for (int j = 0; j < (st ? NI_ST : NI_PM); ++j) {
-            double a = soc ? cs[j] : cr[j] - s[j];
-            for (int q = 0; q < na; ++q) a += jc[j * 8 + q] * dy[st ? c_act_st[q] : c_act_pm[q]];
-            const double dzj = mu / s[j] - z[j] - (z[j] / s[j]) * a;
-            dsl[j] = a; dz[j] = dzj;
-            if (a < 0.0) a_p = fmin(a_p, -tau * s[j] / a);
-            if (dzj < 0.0) a_d = fmin(a_d, -tau * z[j] / dzj);
-            dphi -= mu * a / s[j];
+    // lanes over (stage, inequality row): N*10 SingleTrack rows, then M*2 PointMass rows
+    const int n_rows = N * NI_ST + M * NI_PM;
+    for (int e = lane; e < n_rows; e += 32) {
+        const bool st = e < N * NI_ST;
+        const int k = st ? e / NI_ST : N + (e - N * NI_ST) / NI_PM;
+        const int j = st ? e - k * NI_ST : (e - N * NI_ST) - (k - N) * NI_PM;
+        const double *jc = ws.at(b, W_JC, k) + j * 8, *dy = ws.at(b, soc ? W_DY2 : W_DY, k);
+        const double sj = ws.at(b, W_S, k)[j], zj = ws.at(b, W_Z, k)[j];
+        double a = soc ? ws.at(b, W_CS, k)[j] : ws.at(b, W_CRES, k)[j] - sj;
+        if (st) {
+            double jr[8], dv[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) { jr[q] = jc[q]; dv[q] = dy[c_act_st[q]]; }
+#pragma unroll
+            for (int q = 0; q < 8; ++q) a += jr[q] * dv[q];
+        } else {
+            double jr[5], dv[5];
+#pragma unroll
+            for (int q = 0; q < 5; ++q) { jr[q] = jc[q]; dv[q] = dy[c_act_pm[q]]; }
+#pragma unroll
+            for (int q = 0; q < 5; ++q) a += jr[q] * dv[q];
         }
-        for (int i = 0; i < (st ? 10 : 7); ++i) dphi += gf[i] * dy[i];
+        const double dzj = mu / sj - zj - (zj / sj) * a;
+        ws.at(b, soc ? W_DSL2 : W_DSL, k)[j] = a;
+        ws.at(b, soc ? W_DZ2 : W_DZ, k)[j] = dzj;
+        if (a < 0.0) a_p = fmin(a_p, -tau * sj / a);
+        if (dzj < 0.0) a_d = fmin(a_d, -tau * zj / dzj);
+        dphi -= mu * a / sj;
+    }
+    // objective part of the directional derivative: lanes over (stage, variable)
+    for (int e = lane; e < H * 10; e += 32) {
+        const int k = e / 10, i = e - k * 10;
+        if (i < (k < N ? 10 : 7)) dphi += ws.at(b, W_GF, k)[i] * ws.at(b, soc ? W_DY2 : W_DY, k)[i];
     }
     a_p = warp_min(a_p); a_d = warp_min(a_d); dphi = warp_sum(dphi);
 }
@@ -1243,19 +1265,33 @@ __device__ void step_instance(const Prob& pr, const Ws& ws, WarpSm& sm, int b, i
         }
         return;
     }
-    // ---- accept: primal-dual update with the z safeguard (IPOPT kappa_sigma)
-    for (int k = lane; k < H; k += 32) {
-        const bool st = k < N;
-        double *y = ws.at(b, W_Y, k), *lam = ws.at(b, W_LAM, k), *s = ws.at(b, W_S, k), *z = ws.at(b, W_Z, k);
-        const double *dy = ws.at(b, use_soc ? W_DY2 : W_DY, k), *dl = ws.at(b, use_soc ? W_DLAM2 : W_DLAM, k);
-        const double *dsl = ws.at(b, use_soc ? W_DSL2 : W_DSL, k), *dz = ws.at(b, use_soc ? W_DZ2 : W_DZ, k);
-        for (int i = 0; i < (st ? 10 : 7); ++i) y[i] += alpha * dy[i];
-        for (int i = 0; i < (st ? 8 : 5); ++i) lam[i] += alpha * dl[i];
-        for (int j = 0; j < (st ? NI_ST : NI_PM); ++j) {
-            s[j] += alpha * dsl[j];
-            double zj = z[j] + a_d * dz[j];
-            zj = fmin(fmax(zj, mu / (IpmConst::kappa_sigma * s[j])), IpmConst::kappa_sigma * mu / s[j]);
-            z[j] = zj;
+    // ---- accept: primal-dual update with the z safeguard (IPOPT kappa_sigma).  The iterate [y | lam | s] and the
+    // direction [dy | dlam | dsl] are 28 contiguous doubles of each stage record: lanes run over (stage, element) so
+    // that the loads coalesce and are independent (a lane-per-stage loop serialises 38 global round trips per lane)
+    {
+        const int odir = use_soc ? O_DIR2 : O_DIR;
+        double* rec0 = ws.rec(b, 0);
+#pragma unroll 4
+        for (int e = lane; e < H * 28; e += 32) {
+            const int k = e / 28, i = e - k * 28;
+            const bool st = k < N;
+            const bool used = i < 10 ? i < (st ? 10 : 7) : (i < 18 ? i - 10 < (st ? 8 : 5) : i - 18 < (st ? NI_ST : NI_PM));
+            if (used) {
+                double* r = rec0 + (size_t)k * WS_PER_STAGE;
+                r[O_IT + i] += alpha * r[odir + i];
+            }
+        }
+        __syncwarp();
+#pragma unroll 4
+        for (int e = lane; e < H * 10; e += 32) {
+            const int k = e / 10, j = e - k * 10;
+            if (j < (k < N ? NI_ST : NI_PM)) {
+                double* r = rec0 + (size_t)k * WS_PER_STAGE;
+                const double sj = r[O_IT + 18 + j];
+                double zj = r[O_IT + 28 + j] + a_d * r[odir + 28 + j];
+                zj = fmin(fmax(zj, mu / (IpmConst::kappa_sigma * sj)), IpmConst::kappa_sigma * mu / sj);
+                r[O_IT + 28 + j] = zj;
+            }
         }
     }
     if (lane == 0) {
