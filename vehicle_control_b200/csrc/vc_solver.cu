@@ -92,11 +92,15 @@ static_assert(ws_offset(W_LAM) == O_IT + 10 && ws_offset(W_S) == O_IT + 18 && ws
               ws_offset(W_DLAM) == O_DIR + 10 && ws_offset(W_DSL) == O_DIR + 18 && ws_offset(W_DZ) == O_DIR + 28 &&
               ws_offset(W_DLAM2) == O_DIR2 + 10 && ws_offset(W_DSL2) == O_DIR2 + 18 && ws_offset(W_DZ2) == O_DIR2 + 28,
               "iterate / direction blocks must share one layout");
-constexpr int NSCAL = 64;
+constexpr int NSCAL = 96;
 // scalar block of an instance
 enum Scal { S_MU = 0, S_SF, S_DELTA_LAST, S_THETA0, S_NFILT, S_ACC, S_MODE, S_RESTARTS, S_OBJ, S_ERR, S_ITERS,
             S_STATUS, S_DBG_ALPHA, S_DBG_AP, S_DBG_THETA, S_DBG_DPHI, S_FILT = 16, S_NREST = 48, S_DBG_NAN = 50, S_DBG_THT0, S_DBG_PHT0, S_DBG_PHI, S_DBG_SOC, S_DBG_THT2, S_DBG_AP2, S_SHORT /* theta[16] */, S_FILP = 32 /* phi[16] */ };
 constexpr int FILT_MAX = 16;
+// hand-over block between the two halves of an iteration (k_step_a -> k_step_b)
+enum ScalAB { S_PHASE = 64, S_THETA, S_PHI, S_TRIAL, S_AP, S_AD, S_DPHI, S_MU_NEW, S_NFILT_NEW, S_THETA0_NEW, S_ACC_NEW,
+              S_NSHORT_NEW, S_OBJ_NEW, S_ERR_NEW };
+enum Phase { PH_NONE = 0, PH_SEARCH = 1, PH_RESTORE = 2, PH_FAILED = 3, PH_BADINIT = 4 };
 enum Mode { MODE_INIT = 0, MODE_STEP = 1, MODE_DONE = 2, MODE_REINIT = 3 };
 
 struct Ws {
@@ -1305,6 +1309,273 @@ __device__ void step_instance(const Prob& pr, const Ws& ws, WarpSm& sm, int b, i
     }
 }
 
+__device__ void step_part_a(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int lane) {
+    double* sc = ws.scal(b);
+    const int mode = (int)sc[S_MODE];
+    if (mode == MODE_DONE) return;
+    const int N = pr.N, M = pr.M;
+    const Cfg& c = pr.c;
+    if (lane == 0) sc[S_PHASE] = PH_NONE;
+    const Measures m = finish_gradients(pr, ws, b, lane);
+    const bool finite = isfinite(m.f) && isfinite(m.theta) && isfinite(m.rdmax) && isfinite(m.prim);
+    double mu = sc[S_MU];
+    const double sf = sc[S_SF];
+    if (mode == MODE_INIT || mode == MODE_REINIT) {
+        if (!finite) {   // invalid starting point (NaN / inside an obstacle pole): restoration substitute, else give up
+            const int restarts = (int)sc[S_RESTARTS];
+            if (restarts >= 2) { finalize(pr, ws, b, lane, VC_EVAL_ERROR, m.f, INFINITY); return; }
+            if (lane == 0) sc[S_PHASE] = PH_BADINIT;   // the rollout runs in k_step_b
+            return;
+        }
+        if (mode == MODE_INIT && c.obj_scaling && m.gfmax > IpmConst::max_gradient && lane == 0)
+            sc[S_SF] = IpmConst::max_gradient / m.gfmax;   // gradient-based objective scaling at the initial point
+        init_slacks(pr, ws, b, lane, mu);
+        if (lane == 0) { sc[S_MODE] = MODE_STEP; sc[S_NFILT] = 0; sc[S_THETA0] = -1.0; sc[S_ACC] = 0; }
+        return;
+    }
+    // ---- convergence test (IPOPT overall error E_0) and barrier update
+    const int me = 8 + 8 * (N - 1) + (M > 0 ? 5 * M : 0), mi = NI_ST * N + NI_PM * M;
+    const double sd = fmax(IpmConst::s_max, (m.sumlam + m.sumz) / (me + mi)) / IpmConst::s_max;
+    const double scs = fmax(IpmConst::s_max, m.sumz / mi) / IpmConst::s_max;
+    const double e_dp = fmax(m.rdmax / sd, m.prim);
+    const double err0 = fmax(e_dp, compl_error(pr, ws, b, lane, 0.0) / scs);
+    const double obj = m.f;
+    int iters = (int)sc[S_ITERS];
+    if (!finite) { finalize(pr, ws, b, lane, VC_EVAL_ERROR, obj, INFINITY); return; }
+    if (err0 <= c.tol) { finalize(pr, ws, b, lane, VC_SOLVED, obj, err0); return; }
+    int acc = (err0 <= c.acceptable_tol) ? (int)sc[S_ACC] + 1 : 0;
+    if (acc >= c.acceptable_iter) { finalize(pr, ws, b, lane, VC_ACCEPTABLE, obj, err0); return; }
+    if (iters >= c.max_iter) { finalize(pr, ws, b, lane, VC_MAX_ITER, obj, err0); return; }
+    int nfilt = (int)sc[S_NFILT];
+    const double mu_floor = c.tol / 11.0;
+    while (mu > mu_floor * (1 + 1e-12) &&
+           fmax(e_dp, compl_error(pr, ws, b, lane, mu) / scs) <= IpmConst::kappa_eps * mu) {
+        mu = fmax(mu_floor, fmin(IpmConst::kappa_mu * mu, pow(mu, IpmConst::theta_mu)));
+        nfilt = 0;
+    }
+    // stall escape (stands in for IPOPT's watchdog): several consecutive heavily shortened steps mean the Newton
+    // model of this barrier problem is poor where the iterate sits; the barrier problem need not be solved
+    // accurately for path following, so move on to the next rung
+    int n_short = (int)sc[S_SHORT];
+    if (n_short >= pr.stall_iters && mu > mu_floor * (1 + 1e-12)) {
+        mu = fmax(mu_floor, fmin(IpmConst::kappa_mu * mu, pow(mu, IpmConst::theta_mu)));
+        nfilt = 0; n_short = 0;
+    }
+    // feasibility restoration substitute: a run of heavily shortened steps at an infeasible iterate means the
+    // linearisation is poor there (IPOPT would end up in its restoration phase); project the iterate onto the
+    // dynamics manifold by rolling the models out from x0 under the CURRENT controls and restart the barrier
+    // problem from that point (same mu, cleared filter)
+    if (pr.restore_iters > 0 && n_short >= pr.restore_iters && (int)sc[S_NREST] < 3 && m.theta > 1e-6) {
+        if (lane == 0) { sc[S_PHASE] = PH_RESTORE; sc[S_MU_NEW] = mu; }
+        return;
+    }
+    // all restorations used and the steps are still being cut at an infeasible iterate: give the instance up (IPOPT ends
+    // such runs with "restoration failed"); it would otherwise crawl to max_iter and hold the whole batch's tail
+    if (pr.restore_iters > 0 && (int)sc[S_NREST] >= 3 && n_short >= pr.giveup_iters && m.theta > 1e-6 &&
+        !(mu > mu_floor * (1 + 1e-12))) {
+        finalize(pr, ws, b, lane, VC_LINESEARCH_FAIL, obj, err0);
+        return;
+    }
+    const double tau = fmax(IpmConst::tau_min, 1.0 - mu);
+    const double theta = m.theta, phi = sf * m.f - mu * m.lns;
+    double theta0 = sc[S_THETA0];
+    if (theta0 < 0.0) theta0 = theta;
+    const double theta_min = 1e-4 * fmax(1.0, theta0), theta_max = 1e4 * fmax(1.0, theta0);
+    const double delta_last = sc[S_DELTA_LAST];
+    const bool first_ever = delta_last == 0.0;
+    double trial = 0.0, a_p, a_d, dphi;
+    bool failed = false;
+    // ---- inertia-correcting factorisation (IPOPT delta_w ladder) and the slack / multiplier directions
+    while (!riccati(pr, ws, sm, b, lane, mu, trial, false)) {
+        if (trial == 0.0) trial = first_ever ? 1e-4 : fmax(1e-20, delta_last / 3.0);
+        else trial *= first_ever ? 100.0 : 8.0;
+        if (trial > 1e40) { failed = true; break; }
+    }
+    if (!failed) slack_directions(pr, ws, b, lane, mu, tau, false, a_p, a_d, dphi);
+    if (lane == 0) {
+        sc[S_PHASE] = failed ? PH_FAILED : PH_SEARCH;
+        sc[S_MU_NEW] = mu; sc[S_THETA] = theta; sc[S_PHI] = phi; sc[S_THETA0_NEW] = theta0; sc[S_NFILT_NEW] = nfilt;
+        sc[S_TRIAL] = trial; sc[S_ACC_NEW] = acc; sc[S_NSHORT_NEW] = n_short; sc[S_OBJ_NEW] = obj; sc[S_ERR_NEW] = err0;
+        if (!failed) { sc[S_AP] = a_p; sc[S_AD] = a_d; sc[S_DPHI] = dphi; }
+    }
+    (void)theta_min; (void)theta_max; (void)iters;
+}
+
+__device__ void step_part_b(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int lane) {
+    double* sc = ws.scal(b);
+    const int mode = (int)sc[S_MODE];
+    if (mode == MODE_DONE) return;
+    const int H = pr.H, N = pr.N;
+    const Cfg& c = pr.c;
+    const int phase = (int)sc[S_PHASE];
+    if (phase == PH_NONE) return;
+    if (phase == PH_BADINIT) {   // invalid starting point (NaN / inside an obstacle pole): restoration substitute
+        // (an invalid FIRST point has no gradient to scale by: the repaired point then sets the objective scaling)
+        if (lane == 0) { repair_rollout(pr, ws, b); sc[S_RESTARTS] += 1.0; }
+        return;
+    }
+    const double mu = sc[S_MU_NEW], sf = sc[S_SF];
+    const int iters = (int)sc[S_ITERS];
+    if (phase == PH_RESTORE) {
+        __syncwarp();
+        if (lane == 0) {
+            repair_rollout(pr, ws, b, false);
+            if (pr.restore_check && !rollout_sane(pr, ws, b)) repair_rollout(pr, ws, b, true);   // neutral controls instead
+            sc[S_NREST] += 1.0; sc[S_MODE] = MODE_REINIT; sc[S_SHORT] = 0; sc[S_ITERS] = iters + 1; sc[S_MU] = mu;
+        }
+        for (int k = lane; k < H; k += 32) {
+            double *lam = ws.at(b, W_LAM, k), *s = ws.at(b, W_S, k), *z = ws.at(b, W_Z, k);
+            for (int i = 0; i < 8; ++i) lam[i] = 0.0;
+            for (int j = 0; j < 10; ++j) { s[j] = 1.0; z[j] = 0.0; }
+        }
+        return;
+    }
+    const double obj = sc[S_OBJ_NEW], err0 = sc[S_ERR_NEW];
+    const int acc = (int)sc[S_ACC_NEW], n_short = (int)sc[S_NSHORT_NEW];
+    int nfilt = (int)sc[S_NFILT_NEW];
+    const double theta = sc[S_THETA], phi = sc[S_PHI], theta0 = sc[S_THETA0_NEW];
+    const double tau = fmax(IpmConst::tau_min, 1.0 - mu);
+    const double theta_min = 1e-4 * fmax(1.0, theta0), theta_max = 1e4 * fmax(1.0, theta0);
+    const double delta_last = sc[S_DELTA_LAST];
+    const bool first_ever = delta_last == 0.0;
+    double trial = sc[S_TRIAL], alpha = 0.0, a_d = sc[S_AD], dbg_ap = 0.0, dbg_dphi = 0.0, dbg_tht0 = 0.0, dbg_pht0 = 0.0;
+    int dbg_nan = 0;
+    double dbg_tht2 = 0.0, dbg_ap2 = 0.0;
+    bool accepted = false, failed = phase == PH_FAILED;
+    bool have_dir = true;   // the first direction of this iteration was computed by k_step_a
+    int n_damp = 0;
+    double* filt_t = sc + S_FILT;
+    double* filt_p = sc + S_FILP;
+    bool use_soc = false;
+    // acceptance of a trial point by the filter (IPOPT Alg. A, steps A-5.3/5.4); all lanes hold the same values
+    auto acceptable = [&](double a_test, double tht, double pht, double dphi, bool& augment) -> bool {
+        augment = false;
+        if (tht > theta_max) return false;
+        for (int i = 0; i < nfilt; ++i)
+            if (tht >= filt_t[i] && pht >= filt_p[i]) return false;
+        const bool switching = theta <= theta_min && dphi < 0.0 &&
+                               a_test * pow(-dphi, IpmConst::s_phi) > IpmConst::delta * pow(theta, IpmConst::s_theta);
+        if (switching) {
+            if (pht <= phi + IpmConst::eta_phi * a_test * dphi) return true;
+        } else if (tht <= (1 - IpmConst::gamma_theta) * theta || pht <= phi - IpmConst::gamma_phi * theta) {
+            augment = true;
+            return true;
+        }
+        // steps at the rounding floor: both measures unchanged
+        return fabs(pht - phi) <= 1e-13 * fmax(1.0, fabs(phi)) && tht <= theta + 1e-13;
+    };
+    while (!accepted && !failed) {
+        double a_p = sc[S_AP], dphi = sc[S_DPHI];
+        if (!have_dir) {   // damped re-solve: inertia-correcting factorisation (IPOPT delta_w ladder)
+            while (!riccati(pr, ws, sm, b, lane, mu, trial, false)) {
+                if (trial == 0.0) trial = first_ever ? 1e-4 : fmax(1e-20, delta_last / 3.0);
+                else trial *= first_ever ? 100.0 : 8.0;
+                if (trial > 1e40) { failed = true; break; }
+            }
+            if (failed) break;
+            slack_directions(pr, ws, b, lane, mu, tau, false, a_p, a_d, dphi);
+        }
+        have_dir = false;
+        dbg_ap = a_p; dbg_dphi = dphi;
+        // ---- backtracking filter line search, lanes over stages
+        alpha = a_p;
+        for (int bt = 0; bt < 12 && !accepted; ++bt, alpha *= 0.5) {
+            double ft, tht, lnt;
+            const bool okv = trial_point(pr, ws, b, lane, alpha, false, bt == 0, ft, tht, lnt);
+            if (!okv) ++dbg_nan;
+            if (bt == 0) { dbg_tht0 = tht; dbg_pht0 = sf * ft - mu * lnt; }
+            bool augment = false;
+            if (okv && acceptable(alpha, tht, sf * ft - mu * lnt, dphi, augment)) accepted = true;
+            // ---- second-order correction (IPOPT Alg. A-5.5 .. A-5.9): first trial step rejected and infeasibility
+            // not reduced -> re-solve with c_soc = alpha c(x) + c(x + alpha d), at most 4 times
+            if (!accepted && bt == 0 && okv && tht >= theta && pr.max_soc > 0) {
+                soc_residual(pr, ws, b, lane, alpha, false, true);
+                double theta_soc_old = theta;
+                for (int ps = 0; ps < pr.max_soc; ++ps) {
+                    if (!riccati(pr, ws, sm, b, lane, mu, trial, true)) break;
+                    double a_p2, a_d2, dphi2, ft2, tht2, lnt2;
+                    slack_directions(pr, ws, b, lane, mu, tau, true, a_p2, a_d2, dphi2);
+                    const bool ok2 = trial_point(pr, ws, b, lane, a_p2, true, true, ft2, tht2, lnt2);
+                    if (ps == 0) { dbg_tht2 = ok2 ? tht2 : -1.0; dbg_ap2 = a_p2; }
+                    if (ok2 && acceptable(alpha, tht2, sf * ft2 - mu * lnt2, dphi, augment)) {
+                        accepted = true; use_soc = true; alpha = a_p2; a_d = a_d2;
+                        break;
+                    }
+                    if (!ok2 || tht2 > 0.99 * theta_soc_old) break;
+                    theta_soc_old = tht2;
+                    soc_residual(pr, ws, b, lane, a_p2, true, false);
+                }
+            }
+            if (accepted) {
+                if (augment && nfilt < FILT_MAX) {
+                    if (lane == 0) { filt_t[nfilt] = (1 - IpmConst::gamma_theta) * theta; filt_p[nfilt] = phi - IpmConst::gamma_phi * theta; }
+                    ++nfilt;
+                }
+                break;
+            }
+        }
+        __syncwarp();
+        if (accepted) break;
+        // no acceptable step along this direction: damp it (larger delta_w) and retry; IPOPT would restore here
+        trial = fmax(trial, 1e-4) * 100.0;
+        if (trial > 1e12 || ++n_damp > pr.max_damp) failed = true;
+    }
+    if (failed) {
+        const int restarts = (int)sc[S_RESTARTS];
+        if (restarts >= 2) { finalize(pr, ws, b, lane, VC_LINESEARCH_FAIL, obj, err0); return; }
+        __syncwarp();
+        if (lane == 0) {
+            repair_rollout(pr, ws, b);
+            sc[S_RESTARTS] = restarts + 1; sc[S_MODE] = MODE_REINIT; sc[S_MU] = c.mu_init; sc[S_DELTA_LAST] = 0.0;
+            sc[S_ITERS] = iters + 1;
+        }
+        for (int k = lane; k < H; k += 32) {   // neutral multipliers / slacks for the re-evaluation
+            double *lam = ws.at(b, W_LAM, k), *s = ws.at(b, W_S, k), *z = ws.at(b, W_Z, k);
+            for (int i = 0; i < 8; ++i) lam[i] = 0.0;
+            for (int j = 0; j < 10; ++j) { s[j] = 1.0; z[j] = 0.0; }
+        }
+        return;
+    }
+    // ---- accept: primal-dual update with the z safeguard (IPOPT kappa_sigma).  The iterate [y | lam | s] and the
+    // direction [dy | dlam | dsl] are 28 contiguous doubles of each stage record: lanes run over (stage, element) so
+    // that the loads coalesce and are independent (a lane-per-stage loop serialises 38 global round trips per lane)
+    {
+        const int odir = use_soc ? O_DIR2 : O_DIR;
+        double* rec0 = ws.rec(b, 0);
+#pragma unroll 4
+        for (int e = lane; e < H * 28; e += 32) {
+            const int k = e / 28, i = e - k * 28;
+            const bool st = k < N;
+            const bool used = i < 10 ? i < (st ? 10 : 7) : (i < 18 ? i - 10 < (st ? 8 : 5) : i - 18 < (st ? NI_ST : NI_PM));
+            if (used) {
+                double* r = rec0 + (size_t)k * WS_PER_STAGE;
+                r[O_IT + i] += alpha * r[odir + i];
+            }
+        }
+        __syncwarp();
+#pragma unroll 4
+        for (int e = lane; e < H * 10; e += 32) {
+            const int k = e / 10, j = e - k * 10;
+            if (j < (k < N ? NI_ST : NI_PM)) {
+                double* r = rec0 + (size_t)k * WS_PER_STAGE;
+                const double sj = r[O_IT + 18 + j];
+                double zj = r[O_IT + 28 + j] + a_d * r[odir + 28 + j];
+                zj = fmin(fmax(zj, mu / (IpmConst::kappa_sigma * sj)), IpmConst::kappa_sigma * mu / sj);
+                r[O_IT + 28 + j] = zj;
+            }
+        }
+    }
+    if (lane == 0) {
+        sc[S_SHORT] = (alpha < 0.05 * dbg_ap && !use_soc) ? n_short + 1 : 0;
+        sc[S_MU] = mu; sc[S_NFILT] = nfilt; sc[S_THETA0] = theta0; sc[S_ACC] = acc; sc[S_ITERS] = iters + 1;
+        if (trial > 0.0) sc[S_DELTA_LAST] = trial;
+        sc[S_OBJ] = obj; sc[S_ERR] = err0;
+        sc[S_DBG_THT2] = dbg_tht2; sc[S_DBG_AP2] = dbg_ap2;
+        sc[S_DBG_NAN] = dbg_nan; sc[S_DBG_THT0] = dbg_tht0; sc[S_DBG_PHT0] = dbg_pht0; sc[S_DBG_PHI] = phi; sc[S_DBG_SOC] = use_soc;
+        sc[S_DBG_ALPHA] = alpha; sc[S_DBG_AP] = dbg_ap; sc[S_DBG_THETA] = theta; sc[S_DBG_DPHI] = dbg_dphi;
+    }
+}
+
 __global__ void __launch_bounds__(32 * STEP_WARPS, VC_STEP_MINBLOCKS) k_step(Prob pr, Ws ws, int* next_list, int* next_count) {
     __shared__ WarpSm s_all[STEP_WARPS];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -1314,6 +1585,26 @@ __global__ void __launch_bounds__(32 * STEP_WARPS, VC_STEP_MINBLOCKS) k_step(Pro
     step_instance(pr, ws, s_all[wid], b, lane);
     __syncwarp();
     // survivors form the next pass's compacted list (their order does not influence any instance's result)
+    if (lane == 0 && ws.scal(b)[S_MODE] != (double)MODE_DONE) next_list[atomicAdd(next_count, 1)] = b;
+}
+
+// the two halves of an iteration as separate kernels: the factorisation half needs half the registers of the
+// line-search half (no model code), so it runs at twice the occupancy
+__global__ void __launch_bounds__(32 * STEP_WARPS, 4) k_step_a(Prob pr, Ws ws) {
+    __shared__ WarpSm s_all[STEP_WARPS];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int i = blockIdx.x * STEP_WARPS + wid;
+    if (i >= *pr.act_count) return;
+    step_part_a(pr, ws, s_all[wid], pr.act_list[i], lane);
+}
+__global__ void __launch_bounds__(32 * STEP_WARPS, VC_STEP_MINBLOCKS) k_step_b(Prob pr, Ws ws, int* next_list, int* next_count) {
+    __shared__ WarpSm s_all[STEP_WARPS];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int i = blockIdx.x * STEP_WARPS + wid;
+    if (i >= *pr.act_count) return;
+    const int b = pr.act_list[i];
+    if (ws.scal(b)[S_MODE] != (double)MODE_DONE) step_part_b(pr, ws, s_all[wid], b, lane);
+    __syncwarp();
     if (lane == 0 && ws.scal(b)[S_MODE] != (double)MODE_DONE) next_list[atomicAdd(next_count, 1)] = b;
 }
 
@@ -1421,6 +1712,7 @@ int launch_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_k
     const bool debug = getenv("VC_DEBUG") != nullptr;
     int pass = 0;
     const bool prof = h->profiling != 0;
+    const bool split = !(getenv("VC_SPLIT") && atoi(getenv("VC_SPLIT")) == 0);
     size_t ev = 0;
     auto mark = [&]() {
         if (!prof) return;
@@ -1438,7 +1730,13 @@ int launch_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_k
         if (pr.M > 0) k_eval_pm<<<(unsigned)((t_pm + 127) / 128), 128, 0, st>>>(pr, ws);
         cudaMemsetAsync(counts[1 - cur], 0, sizeof(int), st);
         mark();
-        k_step<<<(n_act + STEP_WARPS - 1) / STEP_WARPS, 32 * STEP_WARPS, 0, st>>>(pr, ws, lists[1 - cur], counts[1 - cur]);
+        if (split) {
+            k_step_a<<<(n_act + STEP_WARPS - 1) / STEP_WARPS, 32 * STEP_WARPS, 0, st>>>(pr, ws);
+            k_step_b<<<(n_act + STEP_WARPS - 1) / STEP_WARPS, 32 * STEP_WARPS, 0, st>>>(pr, ws, lists[1 - cur], counts[1 - cur]);
+            h->launches++;
+        } else {
+            k_step<<<(n_act + STEP_WARPS - 1) / STEP_WARPS, 32 * STEP_WARPS, 0, st>>>(pr, ws, lists[1 - cur], counts[1 - cur]);
+        }
         mark();
         cur = 1 - cur;
         h->launches += pr.M > 0 ? 3 : 2;
