@@ -51,6 +51,8 @@ typedef struct vc_mpc_config {
     int obj_scaling;           /* 1 = gradient-based objective scaling (max gradient 100)       */
     double mu_init;            /* 0.1                                                           */
     double bound_relax;        /* 1e-8                                                          */
+    int warm_rungs;            /* >0: the first iteration starts this many rungs down the barrier ladder (warm starts) */
+    int reserved0;
 } vc_mpc_config;
 
 typedef struct vc_handle vc_handle;

@@ -29,7 +29,8 @@ class MpcConfig(C.Structure):
                                     "w_min", "w_max", "Ux_min", "max_speed", "delta_min", "delta_max",
                                     "ey_min", "ey_max", "V_min", "ey_min_pm", "ey_max_pm",
                                     "tol", "acceptable_tol")]
-                + [("acceptable_iter", C.c_int), ("obj_scaling", C.c_int), ("mu_init", D), ("bound_relax", D)])
+                + [("acceptable_iter", C.c_int), ("obj_scaling", C.c_int), ("mu_init", D), ("bound_relax", D),
+                   ("warm_rungs", C.c_int), ("reserved0", C.c_int)])
 
 
 EXPORTS = {

@@ -11,6 +11,8 @@ Per tick (reference :306-338): parameters ds, kappa from the previous prediction
 """
 from __future__ import annotations
 
+import os
+
 import numpy as np
 import torch
 
@@ -37,6 +39,8 @@ class BatchedCascadedMPC(Controller):
         self.N, self.M = int(self.config.horizon), int(self.config.horizon_pm)
         self.H = self.N + self.M
         self.B = int(batch)
+        self.warm_rungs = int(os.environ.get("VC_WARM_RUNGS", self.config.get("warm_rungs", 0) or 0))
+        self._ticks = 0
         self.engine = engine if engine is not None else Engine(car.config, self.config, car.track)
         if engine is not None:
             self.engine.set_config(self.config)
@@ -57,6 +61,13 @@ class BatchedCascadedMPC(Controller):
     def command(self, states: torch.Tensor) -> torch.Tensor:
         """states [B,8] (device) -> first actions [B,2] (device view of action_prediction[:, :, 0])."""
         e = self.engine
+        # first tick: cold guess, barrier ladder from mu_init; later ticks are warm starts and may enter the ladder
+        # `warm_rungs` rungs down (controller config key, default 0 = the reference's IPOPT behaviour)
+        rungs = self.warm_rungs if self._ticks > 0 else 0
+        if e.cfg.warm_rungs != rungs:
+            e.cfg.warm_rungs = rungs
+            e.set_config(e.cfg)
+        self._ticks += 1
         e.horizon_params(states, self.state_prediction, self.ds, self.kappa)
         e.solve(states, self.kappa, self.ds, self.state_prediction, self.action_prediction,
                 obstacles=self.obstacles, out=self.info)

@@ -123,6 +123,7 @@ struct Prob {   // device-side view of one vc_nmpc_solve call
     Cfg c;
     int B, N, M, H, n_obs;
     int stall_iters;   // consecutive shortened steps before the barrier parameter is forced down
+    double mu_start;   // barrier parameter of the first iteration (mu_init advanced by `warm_rungs` rungs of the ladder)
     int max_soc;       // second-order correction steps per iteration (IPOPT max_soc = 4)
     int restore_check; // 1: a restored trajectory that leaves the widened state bounds is replaced by the neutral rollout
     int max_damp;      // damped re-solves of one iteration's direction before the iterate is restored / given up
@@ -172,7 +173,7 @@ __global__ void k_prepare(Prob pr, Ws ws, int* list0, int* count0) {
     if (k == 0) {
         double* sc = ws.scal(b);
         for (int i = 0; i < NSCAL; ++i) sc[i] = 0.0;
-        sc[S_MU] = pr.c.mu_init; sc[S_SF] = 1.0; sc[S_THETA0] = -1.0; sc[S_MODE] = MODE_INIT; sc[S_STATUS] = -1.0;
+        sc[S_MU] = pr.mu_start; sc[S_SF] = 1.0; sc[S_THETA0] = -1.0; sc[S_MODE] = MODE_INIT; sc[S_STATUS] = -1.0;
     }
 }
 
@@ -1650,6 +1651,14 @@ static int fill_prob(vc_handle* h, Prob& pr, int B, const double* d_x0, const do
     pr.restore_check = getenv("VC_RESTORE_CHECK") ? atoi(getenv("VC_RESTORE_CHECK")) : 1;
     pr.max_damp = getenv("VC_MAXDAMP") ? atoi(getenv("VC_MAXDAMP")) : 8;
     pr.giveup_iters = getenv("VC_GIVEUP") ? atoi(getenv("VC_GIVEUP")) : 24;
+    {   // warm-started solves may enter the monotone barrier ladder a few rungs down: the rungs below are the same
+        // numbers, so the solve ends on the same final rung (and point) as one started at mu_init
+        int rungs = getenv("VC_MU0_RUNGS") ? atoi(getenv("VC_MU0_RUNGS")) : h->cfg.warm_rungs;
+        double mu0 = h->cfg.mu_init;
+        const double mu_floor = h->cfg.tol / 11.0;
+        for (int i = 0; i < rungs; ++i) mu0 = fmax(mu_floor, fmin(IpmConst::kappa_mu * mu0, pow(mu0, IpmConst::theta_mu)));
+        pr.mu_start = mu0;
+    }
     pr.max_soc = getenv("VC_MAXSOC") ? atoi(getenv("VC_MAXSOC")) : 4;
     pr.restore_iters = getenv("VC_RESTORE") ? atoi(getenv("VC_RESTORE")) : 8;
     pr.x0 = d_x0; pr.kappa = d_kappa; pr.ds = d_ds; pr.obst = d_obst;
