@@ -19,6 +19,7 @@ namespace vc {
 
 struct Dual1 { double v, d; };
 struct HDual { double v, a, b, ab; };
+template <int K> struct DualK { double v, d[K]; };
 
 // ---- value access / lifting of a univariate function with known f, f', f'' at g.v
 VC_HD double val(double x) { return x; }
@@ -35,6 +36,8 @@ template <class T> VC_HD T cst(double c);
 template <> VC_HD double cst<double>(double c) { return c; }
 template <> VC_HD Dual1 cst<Dual1>(double c) { return Dual1{c, 0.0}; }
 template <> VC_HD HDual cst<HDual>(double c) { return HDual{c, 0.0, 0.0, 0.0}; }
+template <> VC_HD DualK<2> cst<DualK<2>>(double c) { return DualK<2>{c, {0.0, 0.0}}; }
+template <> VC_HD DualK<4> cst<DualK<4>>(double c) { return DualK<4>{c, {0.0, 0.0, 0.0, 0.0}}; }
 
 // ---- Dual1 arithmetic
 VC_HD Dual1 operator+(const Dual1& x, const Dual1& y) { return {x.v + y.v, x.d + y.d}; }
@@ -63,6 +66,52 @@ VC_HD HDual operator-(double c, const HDual& x) { return {c - x.v, -x.a, -x.b, -
 VC_HD HDual operator*(const HDual& x, double c) { return {x.v * c, x.a * c, x.b * c, x.ab * c}; }
 VC_HD HDual operator*(double c, const HDual& x) { return {x.v * c, x.a * c, x.b * c, x.ab * c}; }
 
+
+// ---- DualK<K>: value + K directional derivatives carried together (the value part and every transcendental are
+// evaluated once for K Jacobian columns; K = 2 / 4 trade registers for fewer redundant evaluations than Dual1)
+template <int K> VC_HD double val(const DualK<K>& x) { return x.v; }
+template <int K> VC_HD DualK<K> lift(const DualK<K>& g, double f0, double f1, double) {
+    DualK<K> r; r.v = f0;
+#pragma unroll
+    for (int i = 0; i < K; ++i) r.d[i] = f1 * g.d[i];
+    return r;
+}
+template <int K> VC_HD DualK<K> operator+(const DualK<K>& x, const DualK<K>& y) {
+    DualK<K> r; r.v = x.v + y.v;
+#pragma unroll
+    for (int i = 0; i < K; ++i) r.d[i] = x.d[i] + y.d[i];
+    return r;
+}
+template <int K> VC_HD DualK<K> operator-(const DualK<K>& x, const DualK<K>& y) {
+    DualK<K> r; r.v = x.v - y.v;
+#pragma unroll
+    for (int i = 0; i < K; ++i) r.d[i] = x.d[i] - y.d[i];
+    return r;
+}
+template <int K> VC_HD DualK<K> operator*(const DualK<K>& x, const DualK<K>& y) {
+    DualK<K> r; r.v = x.v * y.v;
+#pragma unroll
+    for (int i = 0; i < K; ++i) r.d[i] = x.d[i] * y.v + x.v * y.d[i];
+    return r;
+}
+template <int K> VC_HD DualK<K> operator-(const DualK<K>& x) {
+    DualK<K> r; r.v = -x.v;
+#pragma unroll
+    for (int i = 0; i < K; ++i) r.d[i] = -x.d[i];
+    return r;
+}
+template <int K> VC_HD DualK<K> operator+(const DualK<K>& x, double c) { DualK<K> r = x; r.v += c; return r; }
+template <int K> VC_HD DualK<K> operator+(double c, const DualK<K>& x) { DualK<K> r = x; r.v += c; return r; }
+template <int K> VC_HD DualK<K> operator-(const DualK<K>& x, double c) { DualK<K> r = x; r.v -= c; return r; }
+template <int K> VC_HD DualK<K> operator-(double c, const DualK<K>& x) { DualK<K> r = -x; r.v += c; return r; }
+template <int K> VC_HD DualK<K> operator*(const DualK<K>& x, double c) {
+    DualK<K> r; r.v = x.v * c;
+#pragma unroll
+    for (int i = 0; i < K; ++i) r.d[i] = x.d[i] * c;
+    return r;
+}
+template <int K> VC_HD DualK<K> operator*(double c, const DualK<K>& x) { return x * c; }
+
 // ---- elementary functions, written once for all three scalar types
 template <class T> VC_HD T recip(const T& x) {
     const double r = 1.0 / val(x);
@@ -74,6 +123,10 @@ VC_HD Dual1 operator/(double c, const Dual1& y) { return c * recip(y); }
 VC_HD HDual operator/(const HDual& x, const HDual& y) { return x * recip(y); }
 VC_HD HDual operator/(const HDual& x, double c) { return x * (1.0 / c); }
 VC_HD HDual operator/(double c, const HDual& y) { return c * recip(y); }
+
+template <int K> VC_HD DualK<K> operator/(const DualK<K>& x, const DualK<K>& y) { return x * recip(y); }
+template <int K> VC_HD DualK<K> operator/(const DualK<K>& x, double c) { return x * (1.0 / c); }
+template <int K> VC_HD DualK<K> operator/(double c, const DualK<K>& y) { return c * recip(y); }
 
 template <class T> VC_HD T ad_sqrt(const T& x) {
     const double s = sqrt(val(x));

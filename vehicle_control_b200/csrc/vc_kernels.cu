@@ -3,6 +3,10 @@
 // All arithmetic fp64; none of it is a dense contraction, so no tensor cores.
 #include "vc_handle.h"
 #include "vc_model.cuh"
+#include <cstdlib>
+#ifndef VC_JAC_K_DEFAULT
+#define VC_JAC_K_DEFAULT 2
+#endif
 
 namespace vc {
 
@@ -74,6 +78,62 @@ k_rollout_st_jac(Params p, int B, int N, const double* __restrict__ x0, const do
             double* out = AB + bn * 80;
 #pragma unroll
             for (int q = 0; q < 10; ++q) out[q * 8 + j] = tile[g][q * 8 + j];
+        }
+        __syncwarp();
+    }
+}
+
+// K1c: the same with K Jacobian columns per lane (DualK<K>): 8/K lanes per trajectory, so the state values and every
+// transcendental are evaluated 8/K times per step instead of 8 times.
+template <int K>
+__global__ void __launch_bounds__(K1_TPB)
+k_rollout_st_jac_k(Params p, int B, int N, const double* __restrict__ x0, const double* __restrict__ U,
+                   const double* __restrict__ kappa, const double* __restrict__ ds, double* __restrict__ X,
+                   double* __restrict__ AB) {
+    constexpr int L = 8 / K, GROUPS = K1_TPB / L;
+    __shared__ double tile[GROUPS][80];
+    const int g = threadIdx.x / L, j = threadIdx.x % L;
+    const int b = blockIdx.x * GROUPS + g;
+    const bool live = b < B;
+    const int bb = live ? b : B - 1;
+    int cols[K];   // columns of [A|B] owned by this lane, out of 0 1 2 3 5 6 8 9
+#pragma unroll
+    for (int c = 0; c < K; ++c) { const int a = j * K + c; cols[c] = a < 4 ? a : (a < 6 ? a + 1 : a + 2); }
+    double xv[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) xv[i] = x0[(size_t)bb * 8 + i];
+    double* Xb = X + (size_t)bb * (N + 1) * 8;
+    if (live)
+        for (int i = j; i < 8; i += L) Xb[i] = xv[i];
+    for (int n = 0; n < N; ++n) {
+        const size_t bn = (size_t)bb * N + n;
+        DualK<K> x[8], u[2], xn[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            x[i].v = xv[i];
+#pragma unroll
+            for (int c = 0; c < K; ++c) x[i].d[c] = cols[c] == i ? 1.0 : 0.0;
+        }
+        u[0].v = U[bn * 2]; u[1].v = U[bn * 2 + 1];
+#pragma unroll
+        for (int c = 0; c < K; ++c) { u[0].d[c] = cols[c] == 8 ? 1.0 : 0.0; u[1].d[c] = cols[c] == 9 ? 1.0 : 0.0; }
+        st_rk4<true>(p, x, u, kappa[bn], ds[bn], xn);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            xv[i] = xn[i].v;
+#pragma unroll
+            for (int c = 0; c < K; ++c) tile[g][i * 10 + cols[c]] = xn[i].d[c];
+        }
+        if (j == 0) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) { tile[g][i * 10 + 4] = (i == 4) ? 1.0 : 0.0; tile[g][i * 10 + 7] = (i == 7) ? 1.0 : 0.0; }
+        }
+        __syncwarp();
+        if (live) {
+            for (int i = j; i < 8; i += L) Xb[(n + 1) * 8 + i] = xv[i];
+            double* out = AB + bn * 80;
+#pragma unroll
+            for (int q = 0; q < 80 / L; ++q) out[q * L + j] = tile[g][q * L + j];
         }
         __syncwarp();
     }
@@ -347,8 +407,17 @@ int vc_rollout_st(vc_handle* h, int B, int N, const double* d_x0, const double* 
     VC_REQUIRE(h && N >= 0, "vc_rollout_st: bad argument");
     if (B <= 0) return 0;
     if (d_AB) {
-        k_rollout_st_jac<<<(B + K1_GROUPS - 1) / K1_GROUPS, K1_TPB, 0, h->stream>>>(h->params, B, N, d_x0, d_U, d_kappa,
-                                                                                 d_ds, d_X, d_AB);
+        static const int jac_k = getenv("VC_JAC_K") ? atoi(getenv("VC_JAC_K")) : VC_JAC_K_DEFAULT;   // Jacobian columns per lane
+        if (jac_k == 2) {
+            constexpr int G = K1_TPB / 4;
+            k_rollout_st_jac_k<2><<<(B + G - 1) / G, K1_TPB, 0, h->stream>>>(h->params, B, N, d_x0, d_U, d_kappa, d_ds, d_X, d_AB);
+        } else if (jac_k == 4) {
+            constexpr int G = K1_TPB / 2;
+            k_rollout_st_jac_k<4><<<(B + G - 1) / G, K1_TPB, 0, h->stream>>>(h->params, B, N, d_x0, d_U, d_kappa, d_ds, d_X, d_AB);
+        } else {
+            k_rollout_st_jac<<<(B + K1_GROUPS - 1) / K1_GROUPS, K1_TPB, 0, h->stream>>>(h->params, B, N, d_x0, d_U, d_kappa,
+                                                                                     d_ds, d_X, d_AB);
+        }
     } else {
         k_rollout_st<<<(B + 127) / 128, 128, 0, h->stream>>>(h->params, B, N, d_x0, d_U, d_kappa, d_ds, d_X);
     }
