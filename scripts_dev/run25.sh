@@ -1,0 +1,6 @@
+# resumable damped retries: parity tests, then A/B bench against the previous build
+python -m pytest tests -m gpu -q -x > gpurun_out/t25_pytest.log 2>&1
+echo "pytest rc $?" >> gpurun_out/t25_pytest.log
+python bench.py --steps 3 --warmup 3 --no-cpu-baseline --lap-cache gpurun_out/lap_cache.npz > gpurun_out/t25_bench_new.log 2>&1
+VC_LIB_PATH=$PWD/vehicle_control_b200/variants/pre_damp.so python bench.py --steps 3 --warmup 3 --no-cpu-baseline --lap-cache gpurun_out/lap_cache.npz > gpurun_out/t25_bench_old.log 2>&1
+true

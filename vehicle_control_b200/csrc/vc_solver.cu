@@ -99,7 +99,7 @@ enum Scal { S_MU = 0, S_SF, S_DELTA_LAST, S_THETA0, S_NFILT, S_ACC, S_MODE, S_RE
 constexpr int FILT_MAX = 16;
 // hand-over block between the two halves of an iteration (k_step_a -> k_step_b)
 enum ScalAB { S_PHASE = 64, S_THETA, S_PHI, S_TRIAL, S_AP, S_AD, S_DPHI, S_MU_NEW, S_NFILT_NEW, S_THETA0_NEW, S_ACC_NEW,
-              S_NSHORT_NEW, S_OBJ_NEW, S_ERR_NEW };
+              S_NSHORT_NEW, S_OBJ_NEW, S_ERR_NEW, S_DAMP_TRIAL, S_NDAMP };
 enum Phase { PH_NONE = 0, PH_SEARCH = 1, PH_RESTORE = 2, PH_FAILED = 3, PH_BADINIT = 4 };
 enum Mode { MODE_INIT = 0, MODE_STEP = 1, MODE_DONE = 2, MODE_REINIT = 3 };
 
@@ -1384,7 +1384,7 @@ __device__ void step_part_a(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int
     const double theta_min = 1e-4 * fmax(1.0, theta0), theta_max = 1e4 * fmax(1.0, theta0);
     const double delta_last = sc[S_DELTA_LAST];
     const bool first_ever = delta_last == 0.0;
-    double trial = 0.0, a_p, a_d, dphi;
+    double trial = sc[S_DAMP_TRIAL], a_p, a_d, dphi;   // > 0: damped re-solve of this iterate's direction (see k_step_b)
     bool failed = false;
     // ---- inertia-correcting factorisation (IPOPT delta_w ladder) and the slack / multiplier directions
     while (!riccati(pr, ws, sm, b, lane, mu, trial, false)) {
@@ -1423,6 +1423,7 @@ __device__ void step_part_b(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int
             repair_rollout(pr, ws, b, false);
             if (pr.restore_check && !rollout_sane(pr, ws, b)) repair_rollout(pr, ws, b, true);   // neutral controls instead
             sc[S_NREST] += 1.0; sc[S_MODE] = MODE_REINIT; sc[S_SHORT] = 0; sc[S_ITERS] = iters + 1; sc[S_MU] = mu;
+            sc[S_DAMP_TRIAL] = 0.0; sc[S_NDAMP] = 0.0;
         }
         for (int k = lane; k < H; k += 32) {
             double *lam = ws.at(b, W_LAM, k), *s = ws.at(b, W_S, k), *z = ws.at(b, W_Z, k);
@@ -1443,7 +1444,6 @@ __device__ void step_part_b(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int
     int dbg_nan = 0;
     double dbg_tht2 = 0.0, dbg_ap2 = 0.0;
     bool accepted = false, failed = phase == PH_FAILED;
-    bool have_dir = true;   // the first direction of this iteration was computed by k_step_a
     int n_damp = 0;
     double* filt_t = sc + S_FILT;
     double* filt_p = sc + S_FILP;
@@ -1465,18 +1465,8 @@ __device__ void step_part_b(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int
         // steps at the rounding floor: both measures unchanged
         return fabs(pht - phi) <= 1e-13 * fmax(1.0, fabs(phi)) && tht <= theta + 1e-13;
     };
-    while (!accepted && !failed) {
-        double a_p = sc[S_AP], dphi = sc[S_DPHI];
-        if (!have_dir) {   // damped re-solve: inertia-correcting factorisation (IPOPT delta_w ladder)
-            while (!riccati(pr, ws, sm, b, lane, mu, trial, false)) {
-                if (trial == 0.0) trial = first_ever ? 1e-4 : fmax(1e-20, delta_last / 3.0);
-                else trial *= first_ever ? 100.0 : 8.0;
-                if (trial > 1e40) { failed = true; break; }
-            }
-            if (failed) break;
-            slack_directions(pr, ws, b, lane, mu, tau, false, a_p, a_d, dphi);
-        }
-        have_dir = false;
+    while (!accepted && !failed) {   // one direction per pass (computed by k_step_a)
+        const double a_p = sc[S_AP], dphi = sc[S_DPHI];
         dbg_ap = a_p; dbg_dphi = dphi;
         // ---- backtracking filter line search, lanes over stages
         alpha = a_p;
@@ -1517,10 +1507,17 @@ __device__ void step_part_b(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int
         }
         __syncwarp();
         if (accepted) break;
-        // no acceptable step along this direction: damp it (larger delta_w) and retry; IPOPT would restore here
+        // no acceptable step along this direction: damp it (larger delta_w) and retry; IPOPT would restore here.
+        // The re-solve happens in the NEXT pass (k_step_a starts its delta_w ladder at S_DAMP_TRIAL; the iterate is
+        // unchanged, so the evaluation kernels reproduce the same derivatives): a pass never holds the whole batch
+        // for more than one factorisation + one line search of its slowest instance
         trial = fmax(trial, 1e-4) * 100.0;
-        if (trial > 1e12 || ++n_damp > pr.max_damp) failed = true;
+        n_damp = (int)sc[S_NDAMP] + 1;
+        if (trial > 1e12 || n_damp > pr.max_damp) { failed = true; break; }
+        if (lane == 0) { sc[S_DAMP_TRIAL] = trial; sc[S_NDAMP] = n_damp; sc[S_ITERS] = iters + 1; }   // a pass counts against max_iter
+        return;
     }
+    if (lane == 0) { sc[S_DAMP_TRIAL] = 0.0; sc[S_NDAMP] = 0.0; }
     if (failed) {
         const int restarts = (int)sc[S_RESTARTS];
         if (restarts >= 2) { finalize(pr, ws, b, lane, VC_LINESEARCH_FAIL, obj, err0); return; }
