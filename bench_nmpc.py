@@ -230,14 +230,16 @@ def run_nmpc(a, rank, world, local):
     share = [m / max(1e-9, sum(prof["ms"])) for m in prof["ms"]]
     inst_passes = max(1, prof["instance_passes"])          # sum over timed+warm-up passes of the active instances
     fp64_peak = bc.FP64_PEAK_TFLOPS
-    # units per launch: one launch of k_step advances every unfinished instance by one interior-point iteration;
-    # one launch of k_eval_st evaluates N stages of every unfinished instance
+    # units per launch: one launch of k_step (the pair k_step_a -> k_step_b, timed together with CUDA events on the
+    # solve stream) advances every unfinished instance by one interior-point iteration; one launch of k_eval_st
+    # evaluates N stages of every unfinished instance.  ncu_dram_bytes_per_unit: from
+    # profiles/r01_ncu_split_kernels.md (k_step_a 413.8 KB + k_step_b 103.8 KB per instance-iteration)
     kern = {
         "k_step": {"units_per_launch": inst_passes / n_step, "unit": "instance-iteration", "bytes_per_unit": STEP_BYTES(H),
                    "flops_per_unit": N * 4.0e3 + M * 1.5e3 + (N * 0.73e3 + M * 0.1e3), "launch_ms": ms_step / n_step,
-                   "ncu_dram_bytes_per_unit": 338.0e3},
+                   "ncu_dram_bytes_per_unit": 517.6e3},
         "k_eval_st": {"units_per_launch": inst_passes * N / n_st, "unit": "stage evaluation", "bytes_per_unit": EVAL_ST_BYTES,
-                      "flops_per_unit": 15.0e3, "launch_ms": ms_st / n_st, "ncu_dram_bytes_per_unit": 2463.0},
+                      "flops_per_unit": 15.0e3, "launch_ms": ms_st / n_st, "ncu_dram_bytes_per_unit": 2715.0},
     }
     dom = "k_step" if ms_step >= ms_st else "k_eval_st"
     kd = kern[dom]

@@ -1719,6 +1719,7 @@ int launch_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_k
     int pass = 0;
     const bool prof = h->profiling != 0;
     const bool split = !(getenv("VC_SPLIT") && atoi(getenv("VC_SPLIT")) == 0);
+    const bool trace = prof && split && getenv("VC_PASS_TRACE") != nullptr;
     size_t ev = 0;
     auto mark = [&]() {
         if (!prof) return;
@@ -1738,6 +1739,7 @@ int launch_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_k
         mark();
         if (split) {
             k_step_a<<<(n_act + STEP_WARPS - 1) / STEP_WARPS, 32 * STEP_WARPS, 0, st>>>(pr, ws);
+            if (trace) mark();
             k_step_b<<<(n_act + STEP_WARPS - 1) / STEP_WARPS, 32 * STEP_WARPS, 0, st>>>(pr, ws, lists[1 - cur], counts[1 - cur]);
             h->launches++;
         } else {
@@ -1765,13 +1767,15 @@ int launch_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_k
     h->last_passes = pass < max_pass ? pass + 1 : max_pass;
     if (prof) {
         cudaStreamSynchronize(st);
-        for (size_t i = 0; i + 3 < ev; i += 4) {
-            float a, b2, c2;
+        const size_t per = trace ? 5 : 4;   // VC_PASS_TRACE=1 adds an event between the two step kernels
+        for (size_t i = 0; i + per - 1 < ev; i += per) {
+            float a, b2, c2, c3 = 0.f;
             cudaEventElapsedTime(&a, h->prof_events[i], h->prof_events[i + 1]);
             cudaEventElapsedTime(&b2, h->prof_events[i + 1], h->prof_events[i + 2]);
-            cudaEventElapsedTime(&c2, h->prof_events[i + 2], h->prof_events[i + 3]);
+            cudaEventElapsedTime(&c2, h->prof_events[i + 2], h->prof_events[i + per - 1]);
+            if (trace) cudaEventElapsedTime(&c3, h->prof_events[i + 2], h->prof_events[i + 3]);
             h->prof_ms[0] += a; h->prof_ms[1] += b2; h->prof_ms[2] += c2;
-            if (getenv("VC_PASS_TRACE")) fprintf(stderr, "[vc] pass %3zu eval_st %.3f eval_pm %.3f step %.3f ms\n", i / 4, a, b2, c2);
+            if (trace) fprintf(stderr, "[vc] pass %3zu eval_st %.3f eval_pm %.3f step %.3f ms (step_a %.3f)\n", i / per, a, b2, c2, c3);
             h->prof_launches[0]++; h->prof_launches[1] += pr.M > 0; h->prof_launches[2]++;
         }
     }
