@@ -45,6 +45,7 @@ def main():
     print(json.dumps({"config": "C4: cascaded 20+35, shoe, closed-loop lap, lock step", "vehicles": B, "ticks": n,
                       "finished": int(done.sum()), "failed": int(sim.failed.sum()), "total_solves": int(sim.total_solves),
                       "wall_s": el, "solves_per_s": sim.total_solves / el,
+                      "retries": sim.controller.retries,
                       "laptime_s": {"min": float(lt.min()) if len(lt) else None, "median": float(np.median(lt)) if len(lt) else None,
                                     "max": float(lt.max()) if len(lt) else None},
                       "reference_laptime_s_20+25": 44.40}))

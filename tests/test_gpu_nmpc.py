@@ -182,3 +182,36 @@ def test_batched_simulator_lockstep(golden):
     x = sim.x.cpu().numpy()
     assert (np.abs(x[0] - S[12]) / np.maximum(1, np.abs(S[12]))).max() < 1e-6
     assert np.isfinite(x).all() and (x[:, 7] > 0.59).all()
+
+
+@pytest.mark.parametrize("case", ["cascaded_obstacles_shoe_cascaded_155", "race1_shoe_singletrack_393"])
+def test_failed_line_search_is_retried(golden, case):
+    """Closed-loop ticks (found by scripts/lap_parity_all.py, saved in tests/golden/hard_ticks.npz) on which the filter
+    line search stalls without IPOPT's restoration phase -- the CPU oracle stalls on them in the same way.  The
+    controller re-solves such instances from the shifted previous solution, then from the cold guess
+    (`retry_failed`, cascaded_mpc.py mirror); with the retries switched off the failure is reported like the
+    reference reports an IPOPT failure (exception)."""
+    from vehicle_control_b200.simulation.racing import RacingSimulator
+    _, meta = golden
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "hard_ticks.npz"))
+    key = str(z[case + "/key"])
+    m = meta[key]
+    name = key.split("/")[1]
+    for retry in (False, True):
+        cfg = dict(m["config"]); cfg["retry_failed"] = retry
+        np.random.seed(31)
+        sc = {"track_name": m["track"], "controller_names": [name], "obstacles": bool(m["config"].get("obstacles")),
+              "slip_angle_plot": False, "name": "t", "save_gif": False, "save_images": False, "save_data": False,
+              "load": False, "logging": False}
+        sim = RacingSimulator(sc, load_yaml("models/dynamic_car.yaml"), load_yaml(f"environment/{m['track']}.yaml"),
+                              controller_configs=[cfg])
+        ctl, car = sim.controllers[0], sim.cars[0]
+        ctl.state_prediction, ctl.action_prediction = z[case + "/Xw"], z[case + "/Uw"]
+        car.state = type(car.state)(*z[case + "/x0"])
+        if not retry:
+            with pytest.raises(RuntimeError, match="NMPC solve failed"):
+                ctl.command(car.state)
+        else:
+            ctl.command(car.state)
+            assert int(ctl.last_info["status"]) <= 1
+            assert ctl._batched.retries == {"shifted": 1, "cold": 0, "unrecovered": 0}

@@ -40,12 +40,18 @@ class BatchedCascadedMPC(Controller):
         self.H = self.N + self.M
         self.B = int(batch)
         self.warm_rungs = int(os.environ.get("VC_WARM_RUNGS", self.config.get("warm_rungs", 0) or 0))
+        # IPOPT's feasibility-restoration phase is not restated.  An instance whose filter line
+        # search fails is re-solved from the previous solution shifted by one stage, then from the cold guess
+        # (`retry_failed: false` in the controller config = one attempt, failure reported as the reference would raise)
+        self.retry_failed = bool(int(os.environ.get("VC_RETRY_FAILED", int(self.config.get("retry_failed", True)))))
+        self.retries = {"shifted": 0, "cold": 0, "unrecovered": 0}
         self._ticks = 0
         self.engine = engine if engine is not None else Engine(car.config, self.config, car.track)
         if engine is not None:
             self.engine.set_config(self.config)
         e = self.engine
         X, U = cold_guess(self.N, self.H)
+        self._cold = (e.tensor(X[None]), e.tensor(U[None]))
         self.state_prediction = e.tensor(np.repeat(X[None], self.B, 0))      # [B,8,H]
         self.action_prediction = e.tensor(np.repeat(U[None], self.B, 0))     # [B,2,H]
         self.ds, self.kappa = e.empty(self.B, self.H), e.empty(self.B, self.H)
@@ -58,8 +64,10 @@ class BatchedCascadedMPC(Controller):
                 ob = np.repeat(ob[None], self.B, 0)
             self.obstacles = e.tensor(ob) if ob.shape[1] else None
 
-    def command(self, states: torch.Tensor) -> torch.Tensor:
-        """states [B,8] (device) -> first actions [B,2] (device view of action_prediction[:, :, 0])."""
+    def command(self, states: torch.Tensor, active: torch.Tensor = None) -> torch.Tensor:
+        """states [B,8] (device) -> first actions [B,2] (device view of action_prediction[:, :, 0]).
+        `active` [B] bool: instances whose failure is worth a retry (the lock-step simulator passes the vehicles
+        still racing)."""
         e = self.engine
         # first tick: cold guess, barrier ladder from mu_init; later ticks are warm starts and may enter the ladder
         # `warm_rungs` rungs down (controller config key, default 0 = the reference's IPOPT behaviour)
@@ -68,10 +76,52 @@ class BatchedCascadedMPC(Controller):
             e.cfg.warm_rungs = rungs
             e.set_config(e.cfg)
         self._ticks += 1
+        if self.retry_failed:
+            Xw, Uw = self.state_prediction.clone(), self.action_prediction.clone()
         e.horizon_params(states, self.state_prediction, self.ds, self.kappa)
         e.solve(states, self.kappa, self.ds, self.state_prediction, self.action_prediction,
                 obstacles=self.obstacles, out=self.info)
+        if self.retry_failed:
+            self._mask = active
+            if bool(self._failed().any()):
+                self._retry(states, Xw, Uw)
         return self.action_prediction[:, :, 0].contiguous()
+
+    def _failed(self):
+        bad = self.info["status"] > 1
+        return bad if self._mask is None else bad & self._mask
+
+    def _retry(self, states, Xw, Uw):
+        """Second and third attempt for the instances that failed, as a compacted sub-batch."""
+        e, N = self.engine, self.N
+        for kind in ("shifted", "cold"):
+            idx = self._failed().nonzero().squeeze(1)
+            if idx.numel() == 0:
+                return
+            if kind == "shifted":    # SingleTrack columns advance by one stage; the PointMass tail stays
+                X, U = Xw[idx].clone(), Uw[idx].clone()
+                X[:, :, :N - 1] = Xw[idx][:, :, 1:N]
+                U[:, :, :N - 1] = Uw[idx][:, :, 1:N]
+            else:
+                X = self._cold[0].repeat(idx.numel(), 1, 1)
+                U = self._cold[1].repeat(idx.numel(), 1, 1)
+            x = states[idx].contiguous()
+            ds, kap = e.horizon_params(x, X)
+            ob = self.obstacles[idx].contiguous() if self.obstacles is not None else None
+            out = e.solve(x, kap, ds, X, U, obstacles=ob)
+            ok = out["status"] <= 1
+            self.retries[kind] += int(ok.sum())
+            good = idx[ok]
+            self.state_prediction[good] = X[ok]
+            self.action_prediction[good] = U[ok]
+            self.ds[good], self.kappa[good] = ds[ok], kap[ok]
+            for k in self.info:
+                self.info[k][good] = out[k][ok]
+        bad = self._failed()
+        self.retries["unrecovered"] += int(bad.sum())
+        # nothing converged for these: keep the warm start they had (not the failed iterate) for the next tick
+        self.state_prediction[bad] = Xw[bad]
+        self.action_prediction[bad] = Uw[bad]
 
     def get_state_prediction(self) -> torch.Tensor:
         """[B,H,3] global (x, y, psi) of every predicted state (:340-352)."""

@@ -200,7 +200,7 @@ class BatchedRacingSimulator:
         n_active = int(self.active.sum())
         if n_active == 0:
             return 0
-        u = self.controller.command(self.x)
+        u = self.controller.command(self.x, active=self.active)
         self.failed |= self.active & (self.controller.info["status"] > 1)
         xn = self.x.clone()
         e.plant_step(xn, u)
