@@ -237,9 +237,9 @@ def run_nmpc(a, rank, world, local):
     kern = {
         "k_step": {"units_per_launch": inst_passes / n_step, "unit": "instance-iteration", "bytes_per_unit": STEP_BYTES(H),
                    "flops_per_unit": N * 4.0e3 + M * 1.5e3 + (N * 0.73e3 + M * 0.1e3), "launch_ms": ms_step / n_step,
-                   "ncu_dram_bytes_per_unit": 517.6e3},
+                   "ncu_dram_bytes_per_unit": 517.6e3, "executed_flops_per_unit": 458.4e3},
         "k_eval_st": {"units_per_launch": inst_passes * N / n_st, "unit": "stage evaluation", "bytes_per_unit": EVAL_ST_BYTES,
-                      "flops_per_unit": 15.0e3, "launch_ms": ms_st / n_st, "ncu_dram_bytes_per_unit": 2715.0},
+                      "flops_per_unit": 15.0e3, "launch_ms": ms_st / n_st, "ncu_dram_bytes_per_unit": 2715.0, "executed_flops_per_unit": 222.7e3},
     }
     dom = "k_step" if ms_step >= ms_st else "k_eval_st"
     kd = kern[dom]
@@ -253,10 +253,14 @@ def run_nmpc(a, rank, world, local):
             "algorithmic_bytes_per_unit": kd["bytes_per_unit"], "launch_ms": kd["launch_ms"],
             "share_of_step": share[2] if dom == "k_step" else share[0],
             "fp64": {"achieved_tflops": kd["units_per_launch"] * kd["flops_per_unit"] / (kd["launch_ms"] * 1e-3) / 1e12,
+                     "executed_tflops": kd["units_per_launch"] * kd["executed_flops_per_unit"] / (kd["launch_ms"] * 1e-3) / 1e12,
+                     "executed_source": "DFMA x2 + DMUL + DADD thread instructions per unit from the committed ncu captures "
+                                        "(scripts/ncu_flops.py, profiles/r01_flop_counts.md) x this run's units and time",
                      "peak_tflops": fp64_peak, "peak_source": "measured DFMA micro-benchmark (profiles/r01_fp64_peak.txt)"},
             "kernels": {k: {"launch_ms": v["launch_ms"], "units_per_launch": v["units_per_launch"],
                             "hbm_gbs": v["units_per_launch"] * v["bytes_per_unit"] / (v["launch_ms"] * 1e-3) / 1e9,
-                            "fp64_tflops": v["units_per_launch"] * v["flops_per_unit"] / (v["launch_ms"] * 1e-3) / 1e12}
+                            "fp64_tflops": v["units_per_launch"] * v["flops_per_unit"] / (v["launch_ms"] * 1e-3) / 1e12,
+                            "fp64_executed_tflops": v["units_per_launch"] * v["executed_flops_per_unit"] / (v["launch_ms"] * 1e-3) / 1e12}
                         for k, v in kern.items()},
             "whole_solve_fp64": {"achieved_tflops": value / world * solve_flops / 1e12,
                                  "frac": value / world * solve_flops / 1e12 / fp64_peak, "flops_per_solve": solve_flops},
