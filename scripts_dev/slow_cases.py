@@ -18,9 +18,12 @@ ds, kap = eng.horizon_params(x0, X)
 out = eng.solve(x0, kap, ds, X, U, obstacles=ob)
 st, it = out["status"].cpu().numpy(), out["iters"].cpu().numpy()
 print("status counts", np.unique(st, return_counts=True), "iters pct", np.percentile(it, [50, 90, 99, 99.9]))
+for lo in (60, 80, 100, 150, 200, 250, 300):
+    m = it >= lo
+    print(f"iters >= {lo}: {int(m.sum())} instances, of which converged {int((m & (st <= 1)).sum())}")
 order = np.argsort(-it)
-slow_ok = [b for b in order if st[b] == 0][:3]
-fails = [b for b in order if st[b] > 1][:3]
+slow_ok = [b for b in order if st[b] == 0][:4]
+fails = [b for b in order if st[b] > 1][:5]
 np.savez("gpurun_out/slow_cases.npz", b=np.array(slow_ok + fails), x0=x0h[slow_ok + fails], Xw=Xwh[slow_ok + fails],
          Uw=Uwh[slow_ok + fails], ob=obh[slow_ok + fails], tick=idx[slow_ok + fails])
 os.environ["VC_DEBUG"] = "1"

@@ -1402,7 +1402,11 @@ __device__ void step_part_a(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int
     (void)theta_min; (void)theta_max; (void)iters;
 }
 
-__device__ void step_part_b(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int lane) {
+// results of the backtracking trial points alpha = a_p 2^-bt evaluated ahead of time by the other warps of a
+// k_step_b_wide block (nullptr: evaluate them one after the other)
+struct TrialCache { double ok, f, theta, lns; };
+
+__device__ void step_part_b(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int lane, const TrialCache* cache = nullptr) {
     double* sc = ws.scal(b);
     const int mode = (int)sc[S_MODE];
     if (mode == MODE_DONE) return;
@@ -1472,7 +1476,9 @@ __device__ void step_part_b(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int
         alpha = a_p;
         for (int bt = 0; bt < 12 && !accepted; ++bt, alpha *= 0.5) {
             double ft, tht, lnt;
-            const bool okv = trial_point(pr, ws, b, lane, alpha, false, bt == 0, ft, tht, lnt);
+            bool okv;
+            if (cache) { okv = cache[bt].ok != 0.0; ft = cache[bt].f; tht = cache[bt].theta; lnt = cache[bt].lns; }
+            else okv = trial_point(pr, ws, b, lane, alpha, false, bt == 0, ft, tht, lnt);
             if (!okv) ++dbg_nan;
             if (bt == 0) { dbg_tht0 = tht; dbg_pht0 = sf * ft - mu * lnt; }
             bool augment = false;
@@ -1606,6 +1612,34 @@ __global__ void __launch_bounds__(32 * STEP_WARPS, VC_STEP_MINBLOCKS) k_step_b(P
     if (lane == 0 && ws.scal(b)[S_MODE] != (double)MODE_DONE) next_list[atomicAdd(next_count, 1)] = b;
 }
 
+// Late passes hold a handful of instances whose line searches backtrack many times, one trial point after the other,
+// on an otherwise idle GPU.  With few instances left a block of LS_TRIALS warps serves ONE instance: warp w evaluates
+// the trial point alpha = a_p 2^-w speculatively, then warp 0 runs the unchanged acceptance logic on the cached values
+// (the first acceptable alpha in the same order: identical results).
+constexpr int LS_TRIALS = 12;
+__global__ void __launch_bounds__(32 * LS_TRIALS, 1) k_step_b_wide(Prob pr, Ws ws, int* next_list, int* next_count) {
+    __shared__ WarpSm s_one;
+    __shared__ TrialCache s_trial[LS_TRIALS];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if ((int)blockIdx.x >= *pr.act_count) return;
+    const int b = pr.act_list[blockIdx.x];
+    const double* sc = ws.scal(b);
+    const bool live = sc[S_MODE] != (double)MODE_DONE;
+    const bool search = live && (int)sc[S_PHASE] == PH_SEARCH;
+    if (search) {
+        double alpha = sc[S_AP];
+        for (int w = 0; w < wid; ++w) alpha *= 0.5;
+        double ft, tht, lnt;
+        const bool okv = trial_point(pr, ws, b, lane, alpha, false, wid == 0, ft, tht, lnt);
+        if (lane == 0) s_trial[wid] = TrialCache{okv ? 1.0 : 0.0, ft, tht, lnt};
+    }
+    __syncthreads();
+    if (wid != 0) return;
+    if (live) step_part_b(pr, ws, s_one, b, lane, search ? s_trial : nullptr);
+    __syncwarp();
+    if (lane == 0 && ws.scal(b)[S_MODE] != (double)MODE_DONE) next_list[atomicAdd(next_count, 1)] = b;
+}
+
 // k_nmpc_eval: objective / max equality violation / min inequality margin of given trajectories (no solve)
 __global__ void __launch_bounds__(128) k_nmpc_eval(Prob pr, const double* X, const double* U, double* out) {
     const int lane = threadIdx.x & 31;
@@ -1719,6 +1753,7 @@ int launch_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_k
     int pass = 0;
     const bool prof = h->profiling != 0;
     const bool split = !(getenv("VC_SPLIT") && atoi(getenv("VC_SPLIT")) == 0);
+    const int wide_max = getenv("VC_WIDE_MAX") ? atoi(getenv("VC_WIDE_MAX")) : 296;   // <= 2 blocks per SM: one instance per block
     const bool trace = prof && split && getenv("VC_PASS_TRACE") != nullptr;
     size_t ev = 0;
     auto mark = [&]() {
@@ -1740,7 +1775,10 @@ int launch_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_k
         if (split) {
             k_step_a<<<(n_act + STEP_WARPS - 1) / STEP_WARPS, 32 * STEP_WARPS, 0, st>>>(pr, ws);
             if (trace) mark();
-            k_step_b<<<(n_act + STEP_WARPS - 1) / STEP_WARPS, 32 * STEP_WARPS, 0, st>>>(pr, ws, lists[1 - cur], counts[1 - cur]);
+            if (n_act <= wide_max)
+                k_step_b_wide<<<n_act, 32 * LS_TRIALS, 0, st>>>(pr, ws, lists[1 - cur], counts[1 - cur]);
+            else
+                k_step_b<<<(n_act + STEP_WARPS - 1) / STEP_WARPS, 32 * STEP_WARPS, 0, st>>>(pr, ws, lists[1 - cur], counts[1 - cur]);
             h->launches++;
         } else {
             k_step<<<(n_act + STEP_WARPS - 1) / STEP_WARPS, 32 * STEP_WARPS, 0, st>>>(pr, ws, lists[1 - cur], counts[1 - cur]);
