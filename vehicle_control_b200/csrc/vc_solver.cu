@@ -99,7 +99,7 @@ enum Scal { S_MU = 0, S_SF, S_DELTA_LAST, S_THETA0, S_NFILT, S_ACC, S_MODE, S_RE
 constexpr int FILT_MAX = 16;
 // hand-over block between the two halves of an iteration (k_step_a -> k_step_b)
 enum ScalAB { S_PHASE = 64, S_THETA, S_PHI, S_TRIAL, S_AP, S_AD, S_DPHI, S_MU_NEW, S_NFILT_NEW, S_THETA0_NEW, S_ACC_NEW,
-              S_NSHORT_NEW, S_OBJ_NEW, S_ERR_NEW, S_DAMP_TRIAL, S_NDAMP };
+              S_NSHORT_NEW, S_OBJ_NEW, S_ERR_NEW, S_DAMP_TRIAL, S_NDAMP, S_UPD_DIR, S_UPD_ALPHA, S_UPD_AD };
 enum Phase { PH_NONE = 0, PH_SEARCH = 1, PH_RESTORE = 2, PH_FAILED = 3, PH_BADINIT = 4 };
 enum Mode { MODE_INIT = 0, MODE_STEP = 1, MODE_DONE = 2, MODE_REINIT = 3 };
 
@@ -1540,35 +1540,9 @@ __device__ void step_part_b(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int
         }
         return;
     }
-    // ---- accept: primal-dual update with the z safeguard (IPOPT kappa_sigma).  The iterate [y | lam | s] and the
-    // direction [dy | dlam | dsl] are 28 contiguous doubles of each stage record: lanes run over (stage, element) so
-    // that the loads coalesce and are independent (a lane-per-stage loop serialises 38 global round trips per lane)
-    {
-        const int odir = use_soc ? O_DIR2 : O_DIR;
-        double* rec0 = ws.rec(b, 0);
-#pragma unroll 4
-        for (int e = lane; e < H * 28; e += 32) {
-            const int k = e / 28, i = e - k * 28;
-            const bool st = k < N;
-            const bool used = i < 10 ? i < (st ? 10 : 7) : (i < 18 ? i - 10 < (st ? 8 : 5) : i - 18 < (st ? NI_ST : NI_PM));
-            if (used) {
-                double* r = rec0 + (size_t)k * WS_PER_STAGE;
-                r[O_IT + i] += alpha * r[odir + i];
-            }
-        }
-        __syncwarp();
-#pragma unroll 4
-        for (int e = lane; e < H * 10; e += 32) {
-            const int k = e / 10, j = e - k * 10;
-            if (j < (k < N ? NI_ST : NI_PM)) {
-                double* r = rec0 + (size_t)k * WS_PER_STAGE;
-                const double sj = r[O_IT + 18 + j];
-                double zj = r[O_IT + 28 + j] + a_d * r[odir + 28 + j];
-                zj = fmin(fmax(zj, mu / (IpmConst::kappa_sigma * sj)), IpmConst::kappa_sigma * mu / sj);
-                r[O_IT + 28 + j] = zj;
-            }
-        }
-    }
+    // ---- accept: the primal-dual update itself is streaming work (38 doubles per stage read twice, written once) and
+    // runs in k_update at full occupancy; here only its parameters are handed over
+    if (lane == 0) { sc[S_UPD_DIR] = use_soc ? 2.0 : 1.0; sc[S_UPD_ALPHA] = alpha; sc[S_UPD_AD] = a_d; }
     if (lane == 0) {
         sc[S_SHORT] = (alpha < 0.05 * dbg_ap && !use_soc) ? n_short + 1 : 0;
         sc[S_MU] = mu; sc[S_NFILT] = nfilt; sc[S_THETA0] = theta0; sc[S_ACC] = acc; sc[S_ITERS] = iters + 1;
@@ -1607,6 +1581,8 @@ __global__ void __launch_bounds__(32 * STEP_WARPS, VC_STEP_MINBLOCKS) k_step_b(P
     const int i = blockIdx.x * STEP_WARPS + wid;
     if (i >= *pr.act_count) return;
     const int b = pr.act_list[i];
+    if (lane == 0) ws.scal(b)[S_UPD_DIR] = 0.0;
+    __syncwarp();
     if (ws.scal(b)[S_MODE] != (double)MODE_DONE) step_part_b(pr, ws, s_all[wid], b, lane);
     __syncwarp();
     if (lane == 0 && ws.scal(b)[S_MODE] != (double)MODE_DONE) next_list[atomicAdd(next_count, 1)] = b;
@@ -1635,9 +1611,40 @@ __global__ void __launch_bounds__(32 * LS_TRIALS, 1) k_step_b_wide(Prob pr, Ws w
     }
     __syncthreads();
     if (wid != 0) return;
+    if (lane == 0) ws.scal(b)[S_UPD_DIR] = 0.0;
+    __syncwarp();
     if (live) step_part_b(pr, ws, s_one, b, lane, search ? s_trial : nullptr);
     __syncwarp();
     if (lane == 0 && ws.scal(b)[S_MODE] != (double)MODE_DONE) next_list[atomicAdd(next_count, 1)] = b;
+}
+
+// Accepted step of every instance of the pass: one warp per (instance, stage).  Lane i < 28 owns element i of the
+// contiguous [y 10 | lam 8 | s 10] row, lanes 18..27 also update the multiplier z of the slack they hold, with the
+// kappa_sigma safeguard of IPOPT (same arithmetic as the in-kernel update of the fused k_step).
+__global__ void __launch_bounds__(128) k_update(Prob pr, Ws ws) {
+    const int lane = threadIdx.x & 31;
+    const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int H = pr.H;
+    const int ii = (int)(w / H), k = (int)(w - (long long)ii * H);
+    if (ii >= *pr.act_count) return;
+    const int b = pr.act_list[ii];
+    const double* sc = ws.scal(b);
+    const int dir = (int)sc[S_UPD_DIR];
+    if (dir == 0) return;
+    const double alpha = sc[S_UPD_ALPHA], a_d = sc[S_UPD_AD], mu = sc[S_MU];
+    const int odir = dir == 2 ? O_DIR2 : O_DIR;
+    const bool st = k < pr.N;
+    const int i = lane, j = lane - 18;
+    const int lim = i < 10 ? (st ? 10 : 7) : (i < 18 ? (st ? 18 : 15) : 18 + (st ? NI_ST : NI_PM));
+    if (i >= lim) return;
+    double* r = ws.rec(b, k);
+    const double v = r[O_IT + i] + alpha * r[odir + i];
+    r[O_IT + i] = v;
+    if (j >= 0) {
+        double zj = r[O_IT + 28 + j] + a_d * r[odir + 28 + j];
+        zj = fmin(fmax(zj, mu / (IpmConst::kappa_sigma * v)), IpmConst::kappa_sigma * mu / v);
+        r[O_IT + 28 + j] = zj;
+    }
 }
 
 // k_nmpc_eval: objective / max equality violation / min inequality margin of given trajectories (no solve)
@@ -1779,7 +1786,8 @@ int launch_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_k
                 k_step_b_wide<<<n_act, 32 * LS_TRIALS, 0, st>>>(pr, ws, lists[1 - cur], counts[1 - cur]);
             else
                 k_step_b<<<(n_act + STEP_WARPS - 1) / STEP_WARPS, 32 * STEP_WARPS, 0, st>>>(pr, ws, lists[1 - cur], counts[1 - cur]);
-            h->launches++;
+            k_update<<<(unsigned)(((long long)n_act * pr.H * 32 + 127) / 128), 128, 0, st>>>(pr, ws);
+            h->launches += 2;
         } else {
             k_step<<<(n_act + STEP_WARPS - 1) / STEP_WARPS, 32 * STEP_WARPS, 0, st>>>(pr, ws, lists[1 - cur], counts[1 - cur]);
         }
