@@ -94,8 +94,13 @@ def run_rollout(a, rank, world, local):
         "e2e": {"value": world * Be * N * a.steps / e2e_s, "unit": "state-steps/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "trajectories_per_step": Be},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "peak_source": how, "kernel": "k_rollout_st_jac",
-                     "fp64_gflops_algorithmic": B * N * FLOPS_PER_STEP / (kern_ms * 1e-3) / 1e9},
+                     # ncu --set full of k_rollout_st_jac_k<2> (profiles/r01_ncu_rollout_k2.md): 744.2 B of DRAM traffic
+                     # and 12.83 kflop executed (DFMA x2 + DMUL + DADD) per state-step
+                     "traffic": B * N * 744.2, "peak_source": how, "kernel": "k_rollout_st_jac_k<2>",
+                     "traffic_source": "dram__bytes_read+write per state-step from the committed ncu capture x this run's units",
+                     "fp64_gflops_algorithmic": B * N * FLOPS_PER_STEP / (kern_ms * 1e-3) / 1e9,
+                     "fp64_gflops_executed": B * N * 12.83e3 / (kern_ms * 1e-3) / 1e9,
+                     "fp64_peak_gflops": bc.FP64_PEAK_TFLOPS * 1e3},
     }
     if rank == 0 and not a.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline_rollout(tr, states, N)
