@@ -103,6 +103,17 @@ int vc_rollout_pm(vc_handle* h, int B, int M, const double* d_x0, const double* 
 /* replaces: RacingCar.drive (racing_car.py:34-46): kappa = k(s); x <- RK4_t(x,u,kappa,dt) in place. */
 int vc_plant_step(vc_handle* h, int B, double* d_x, const double* d_u, double dt);
 
+/* Per-instance tracks (the reference builds ONE Track per simulation, track.py:84-167): an atlas of
+ * the curvature splines of several tracks (Track.k of each, track.py:156-167).  h_coefs = the tables concatenated,
+ * h_offsets[n_tracks+1] their extents, h_x0 / h_step the uniform sites of each table (host pointers, copied once).
+ * vc_horizon_params_tracks / vc_plant_step_tracks = vc_horizon_params / vc_plant_step with the table of
+ * d_track_id[b] (int32, device) for instance b; same arithmetic, bit for bit. */
+int vc_set_track_atlas(vc_handle* h, int n_tracks, const double* h_coefs, const int* h_offsets, const double* h_x0,
+                       const double* h_step);
+int vc_horizon_params_tracks(vc_handle* h, int B, const int* d_track_id, const double* d_x0, const double* d_Xprev,
+                             double* d_ds, double* d_kappa);
+int vc_plant_step_tracks(vc_handle* h, int B, const int* d_track_id, double* d_x, const double* d_u, double dt);
+
 /* replaces: the tyre helper Functions car.Fx_f/Fx_r/Fy_f/Fy_r/alpha_f/alpha_r (dynamic_car.py:79-142)
  * for arrays.  d_out[B,6] = Fx_f Fx_r Fy_f Fy_r alpha_f alpha_r. */
 int vc_tyre_forces(vc_handle* h, int B, const double* d_x, const double* d_u, double* d_out);

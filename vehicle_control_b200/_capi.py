@@ -47,6 +47,9 @@ EXPORTS = {
     "vc_rollout_st": (C.c_int, [C.c_void_p, C.c_int, C.c_int, PD, PD, PD, PD, PD, PD]),
     "vc_rollout_pm": (C.c_int, [C.c_void_p, C.c_int, C.c_int, PD, PD, PD, PD, PD, PD]),
     "vc_plant_step": (C.c_int, [C.c_void_p, C.c_int, PD, PD, D]),
+    "vc_set_track_atlas": (C.c_int, [C.c_void_p, C.c_int, PD, PD, PD, PD]),
+    "vc_horizon_params_tracks": (C.c_int, [C.c_void_p, C.c_int, PD, PD, PD, PD, PD]),
+    "vc_plant_step_tracks": (C.c_int, [C.c_void_p, C.c_int, PD, PD, PD, D]),
     "vc_tyre_forces": (C.c_int, [C.c_void_p, C.c_int, PD, PD, PD]),
     "vc_nmpc_solve": (C.c_int, [C.c_void_p, C.c_int, PD, PD, PD, PD, C.c_int, PD, PD, PD, PD, PD, PD]),
     "vc_nmpc_eval": (C.c_int, [C.c_void_p, C.c_int, PD, PD, PD, PD, C.c_int, PD, PD, PD]),

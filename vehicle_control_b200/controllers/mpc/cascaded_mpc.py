@@ -45,6 +45,7 @@ class BatchedCascadedMPC(Controller):
         # (`retry_failed: false` in the controller config = one attempt, failure reported as the reference would raise)
         self.retry_failed = bool(int(os.environ.get("VC_RETRY_FAILED", int(self.config.get("retry_failed", True)))))
         self.retries = {"shifted": 0, "cold": 0, "unrecovered": 0}
+        self.track_id = None
         self._ticks = 0
         self.engine = engine if engine is not None else Engine(car.config, self.config, car.track)
         if engine is not None:
@@ -64,6 +65,11 @@ class BatchedCascadedMPC(Controller):
                 ob = np.repeat(ob[None], self.B, 0)
             self.obstacles = e.tensor(ob) if ob.shape[1] else None
 
+    def set_tracks(self, tracks, track_id):
+        """Per-instance tracks: instance b drives on tracks[track_id[b]]."""
+        self.engine.set_track_atlas(tracks)
+        self.track_id = torch.as_tensor(np.asarray(track_id), dtype=torch.int32).to(self.engine.device).contiguous()
+
     def command(self, states: torch.Tensor, active: torch.Tensor = None) -> torch.Tensor:
         """states [B,8] (device) -> first actions [B,2] (device view of action_prediction[:, :, 0]).
         `active` [B] bool: instances whose failure is worth a retry (the lock-step simulator passes the vehicles
@@ -78,7 +84,7 @@ class BatchedCascadedMPC(Controller):
         self._ticks += 1
         if self.retry_failed:
             Xw, Uw = self.state_prediction.clone(), self.action_prediction.clone()
-        e.horizon_params(states, self.state_prediction, self.ds, self.kappa)
+        e.horizon_params(states, self.state_prediction, self.ds, self.kappa, track_id=self.track_id)
         e.solve(states, self.kappa, self.ds, self.state_prediction, self.action_prediction,
                 obstacles=self.obstacles, out=self.info)
         if self.retry_failed:
@@ -106,7 +112,7 @@ class BatchedCascadedMPC(Controller):
                 X = self._cold[0].repeat(idx.numel(), 1, 1)
                 U = self._cold[1].repeat(idx.numel(), 1, 1)
             x = states[idx].contiguous()
-            ds, kap = e.horizon_params(x, X)
+            ds, kap = e.horizon_params(x, X, track_id=None if self.track_id is None else self.track_id[idx].contiguous())
             ob = self.obstacles[idx].contiguous() if self.obstacles is not None else None
             out = e.solve(x, kap, ds, X, U, obstacles=ob)
             ok = out["status"] <= 1

@@ -18,6 +18,10 @@ struct vc_handle {
     double* d_yc = nullptr;
     int n_xy = 0;
     double length = 0.0;
+    // track atlas (device): several curvature tables, one per track id (per-instance tracks)
+    double* d_atlas = nullptr;     // concatenated curvature spline coefficients
+    void* d_atlas_desc = nullptr;  // [n_atlas] descriptors {x0, dx, offset, n}
+    int n_atlas = 0;
     int sm_count = 148;
     int max_smem_optin = 0;
     long long launches = 0;

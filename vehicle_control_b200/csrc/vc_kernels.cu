@@ -263,6 +263,62 @@ k_plant_step(Params p, int B, const double* __restrict__ kc, UniformKnots kt, do
     for (int i = 0; i < 8; ++i) x[(size_t)b * 8 + i] = xn[i];
 }
 
+// ---- per-instance tracks: a track atlas holds the curvature tables of several tracks; every
+// instance carries a track id.  Same arithmetic as k_horizon_params / k_plant_step, the table chosen per instance.
+struct TrackDesc { double x0, dx; int off, n; };
+
+__global__ void __launch_bounds__(256)
+k_horizon_params_atlas(int B, int N, int M, double mpc_dt, double ds_pm, const double* __restrict__ atlas,
+                       const TrackDesc* __restrict__ desc, int n_tracks, const int* __restrict__ track_id,
+                       const double* __restrict__ x0, const double* __restrict__ Xprev, double* __restrict__ ds,
+                       double* __restrict__ kappa) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    const int H = N + M;
+    const int tid = min(max(track_id[b], 0), n_tracks - 1);
+    const TrackDesc td = desc[tid];
+    const UniformKnots kt{td.x0, td.dx, td.n};
+    const double* c = atlas + td.off;
+    const double* ux = Xprev + (size_t)b * 8 * H;
+    double* dsb = ds + (size_t)b * H;
+    double* kb = kappa + (size_t)b * H;
+    const double s0 = x0[(size_t)b * 8 + IS];
+    double cum = 0.0, d0 = 0.0, dlast = 0.0, slast = s0;
+    for (int n = 0; n < N; ++n) {
+        const double d = mpc_dt * ux[n];
+        if (n == 0) d0 = d;
+        cum += d;
+        const double s = cum - d0 + s0;
+        dsb[n] = d;
+        kb[n] = bspline3(c, kt, s, nullptr);
+        dlast = d; slast = s;
+    }
+    double cum_pm = 0.0;
+    for (int m = 0; m < M; ++m) {
+        cum_pm += ds_pm;
+        const double s = cum_pm - dlast + slast;
+        dsb[N + m] = ds_pm;
+        kb[N + m] = bspline3(c, kt, s, nullptr);
+    }
+}
+
+__global__ void __launch_bounds__(128)
+k_plant_step_atlas(Params p, int B, const double* __restrict__ atlas, const TrackDesc* __restrict__ desc, int n_tracks,
+                   const int* __restrict__ track_id, double* __restrict__ x, const double* __restrict__ u, double dt) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    const int tid = min(max(track_id[b], 0), n_tracks - 1);
+    const TrackDesc td = desc[tid];
+    double xv[8], xn[8], uv[2];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) xv[i] = x[(size_t)b * 8 + i];
+    uv[0] = u[(size_t)b * 2]; uv[1] = u[(size_t)b * 2 + 1];
+    const double kp = bspline3(atlas + td.off, UniformKnots{td.x0, td.dx, td.n}, xv[IS], nullptr);
+    st_rk4<false>(p, xv, uv, kp, dt, xn);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) x[(size_t)b * 8 + i] = xn[i];
+}
+
 __global__ void k_tyre_forces(Params p, int B, const double* __restrict__ x, const double* __restrict__ u,
                               double* __restrict__ out) {
     const int b = blockIdx.x * blockDim.x + threadIdx.x;
@@ -328,6 +384,7 @@ int vc_destroy(vc_handle* h) {
     if (!h) return 0;
     cudaSetDevice(h->device);
     cudaFree(h->d_kc); cudaFree(h->d_xc); cudaFree(h->d_yc); cudaFree(h->d_scratch);
+    cudaFree(h->d_atlas); cudaFree(h->d_atlas_desc);
     cudaFree(h->d_ws); cudaFree(h->d_active);
     if (h->h_active) cudaFreeHost(h->h_active);
     delete h;
@@ -439,6 +496,53 @@ int vc_plant_step(vc_handle* h, int B, double* d_x, const double* d_u, double dt
     if (B <= 0) return 0;
     k_plant_step<<<(B + 127) / 128, 128, 0, h->stream>>>(h->params, B, h->d_kc, kknots(h), d_x, d_u, dt);
     VC_LAUNCH_CHECK(h, "k_plant_step");
+    return 0;
+}
+
+int vc_set_track_atlas(vc_handle* h, int n_tracks, const double* h_coefs, const int* h_offsets, const double* h_x0,
+                       const double* h_step) {
+    VC_REQUIRE(h && n_tracks >= 1 && h_coefs && h_offsets && h_x0 && h_step, "vc_set_track_atlas: bad argument");
+    cudaSetDevice(h->device);
+    cudaFree(h->d_atlas); cudaFree(h->d_atlas_desc);
+    h->d_atlas = nullptr; h->d_atlas_desc = nullptr; h->n_atlas = 0;
+    std::vector<TrackDesc> desc(n_tracks);
+    for (int t = 0; t < n_tracks; ++t) {
+        const int n = h_offsets[t + 1] - h_offsets[t];
+        VC_REQUIRE(n >= 8 && h_step[t] > 0, "vc_set_track_atlas: bad curvature table");
+        desc[t] = TrackDesc{h_x0[t], h_step[t], h_offsets[t], n};
+    }
+    const size_t total = (size_t)h_offsets[n_tracks];
+    int rc = check_cuda(cudaMalloc(&h->d_atlas, sizeof(double) * total), "cudaMalloc(track atlas)");
+    if (rc) return rc;
+    rc = check_cuda(cudaMalloc(&h->d_atlas_desc, sizeof(TrackDesc) * n_tracks), "cudaMalloc(track atlas)");
+    if (rc) return rc;
+    cudaMemcpy(h->d_atlas, h_coefs, sizeof(double) * total, cudaMemcpyHostToDevice);
+    rc = check_cuda(cudaMemcpy(h->d_atlas_desc, desc.data(), sizeof(TrackDesc) * n_tracks, cudaMemcpyHostToDevice),
+                    "cudaMemcpy(track atlas)");
+    if (rc) return rc;
+    h->n_atlas = n_tracks;
+    return 0;
+}
+
+int vc_horizon_params_tracks(vc_handle* h, int B, const int* d_track_id, const double* d_x0, const double* d_Xprev,
+                             double* d_ds, double* d_kappa) {
+    VC_REQUIRE(h && h->n_atlas > 0 && d_track_id, "vc_horizon_params_tracks: track atlas not set");
+    VC_REQUIRE(h->cfg.N >= 1, "vc_horizon_params_tracks: config not set");
+    if (B <= 0) return 0;
+    k_horizon_params_atlas<<<(B + 255) / 256, 256, 0, h->stream>>>(B, h->cfg.N, h->cfg.M, h->cfg.mpc_dt, h->cfg.ds_pm,
+                                                                 h->d_atlas, (const TrackDesc*)h->d_atlas_desc,
+                                                                 h->n_atlas, d_track_id, d_x0, d_Xprev, d_ds, d_kappa);
+    VC_LAUNCH_CHECK(h, "k_horizon_params_atlas");
+    return 0;
+}
+
+int vc_plant_step_tracks(vc_handle* h, int B, const int* d_track_id, double* d_x, const double* d_u, double dt) {
+    VC_REQUIRE(h && h->n_atlas > 0 && d_track_id, "vc_plant_step_tracks: track atlas not set");
+    if (B <= 0) return 0;
+    k_plant_step_atlas<<<(B + 127) / 128, 128, 0, h->stream>>>(h->params, B, h->d_atlas,
+                                                            (const TrackDesc*)h->d_atlas_desc, h->n_atlas, d_track_id,
+                                                            d_x, d_u, dt);
+    VC_LAUNCH_CHECK(h, "k_plant_step_atlas");
     return 0;
 }
 

@@ -104,6 +104,18 @@ class Engine:
                                     yc.ctypes.data, len(xc), t["length"]), "vc_set_track")
         self.track = track
 
+    def set_track_atlas(self, tracks):
+        """Per-instance tracks: upload the curvature tables of several tracks; instance b then names its track by
+        `track_id[b]` in horizon_params / plant_step (include/vc_api.h: vc_set_track_atlas)."""
+        tabs = [t.device_tables() for t in tracks]
+        coefs = np.ascontiguousarray(np.concatenate([t["k_coefs"] for t in tabs]), dtype=np.float64)
+        off = np.ascontiguousarray(np.cumsum([0] + [len(t["k_coefs"]) for t in tabs]), dtype=np.int32)
+        x0 = np.ascontiguousarray([t["k_x0"] for t in tabs], dtype=np.float64)
+        step = np.ascontiguousarray([t["k_step"] for t in tabs], dtype=np.float64)
+        check(self.lib.vc_set_track_atlas(self._h, len(tabs), coefs.ctypes.data, off.ctypes.data, x0.ctypes.data,
+                                          step.ctypes.data), "vc_set_track_atlas")
+        self.tracks = list(tracks)
+
     @property
     def H(self):
         return self.cfg.N + self.cfg.M
@@ -150,9 +162,15 @@ class Engine:
               "vc_rollout_pm")
         return (X, AB) if jac else X
 
-    def plant_step(self, x, u, dt=None):
-        """In-place closed-loop plant step of every vehicle (racing_car.py:34-46)."""
+    def plant_step(self, x, u, dt=None, track_id=None):
+        """In-place closed-loop plant step of every vehicle (racing_car.py:34-46); `track_id` [B] int32 selects the
+        track of each vehicle from the atlas (set_track_atlas)."""
         B = x.shape[0]
+        if track_id is not None:
+            check(self.lib.vc_plant_step_tracks(self._h, B, self._p(track_id, (B,), dtype=torch.int32), self._p(x, (B, 8)),
+                                                self._p(u, (B, 2)), float(self.params.dt if dt is None else dt)),
+                  "vc_plant_step_tracks")
+            return x
         check(self.lib.vc_plant_step(self._h, B, self._p(x, (B, 8)), self._p(u, (B, 2)),
                                      float(self.params.dt if dt is None else dt)), "vc_plant_step")
         return x
@@ -176,10 +194,15 @@ class Engine:
         check(self.lib.vc_rel2glob(self._h, n, self._p(s), self._p(ey), self._p(epsi), self._p(out)), "vc_rel2glob")
         return out
 
-    def horizon_params(self, x0, Xprev, ds=None, kappa=None):
+    def horizon_params(self, x0, Xprev, ds=None, kappa=None, track_id=None):
         B, H = x0.shape[0], self.H
         ds = self.empty(B, H) if ds is None else ds
         kappa = self.empty(B, H) if kappa is None else kappa
+        if track_id is not None:
+            check(self.lib.vc_horizon_params_tracks(self._h, B, self._p(track_id, (B,), dtype=torch.int32),
+                                                    self._p(x0, (B, 8)), self._p(Xprev, (B, 8, H)),
+                                                    self._p(ds, (B, H)), self._p(kappa, (B, H))), "vc_horizon_params_tracks")
+            return ds, kappa
         check(self.lib.vc_horizon_params(self._h, B, self._p(x0, (B, 8)), self._p(Xprev, (B, 8, H)),
                                          self._p(ds, (B, H)), self._p(kappa, (B, H))), "vc_horizon_params")
         return ds, kappa

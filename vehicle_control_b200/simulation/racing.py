@@ -176,7 +176,8 @@ class RacingSimulator:
 class BatchedRacingSimulator:
     """B vehicles, one controller configuration, lock-step ticks, device resident (BASELINE config C4)."""
 
-    def __init__(self, carconfig, trackconfig, controller_config, x0, obstacles=None, device=None, record=True):
+    def __init__(self, carconfig, trackconfig, controller_config, x0, obstacles=None, device=None, record=True,
+                 tracks=None, track_id=None):
         self.track = trackconfig if isinstance(trackconfig, Track) else Track(trackconfig)
         self.config = as_config(controller_config)
         self.engine = Engine(as_config(carconfig), self.config, self.track, device=device)
@@ -186,6 +187,13 @@ class BatchedRacingSimulator:
         car = DynamicCar(carconfig, self.track, engine=e)
         self.controller = BatchedCascadedMPC(car, None, self.config, self.B, engine=e, obstacles=obstacles)
         self.x = e.tensor(x0)
+        # per-vehicle tracks: `tracks` (list of Track) and `track_id` [B]; the finish line is each vehicle's own
+        self.track_id = None
+        self.lengths = torch.full((self.B,), float(self.track.length), dtype=torch.float64, device=e.device)
+        if tracks is not None:
+            self.controller.set_tracks(tracks, track_id)
+            self.track_id = self.controller.track_id
+            self.lengths = e.tensor(np.array([tracks[int(i)].length for i in np.asarray(track_id)], dtype=float))
         self.active = torch.ones(self.B, dtype=torch.bool, device=e.device)
         self.ticks = torch.zeros(self.B, dtype=torch.int32, device=e.device)
         self.failed = torch.zeros(self.B, dtype=torch.bool, device=e.device)
@@ -196,14 +204,14 @@ class BatchedRacingSimulator:
     def update(self) -> int:
         """One lock-step tick.  Vehicles past the finish line (or whose solve failed) keep their state."""
         e = self.engine
-        self.active &= ~(self.x[:, 4] > self.track.length - 0.1) & ~self.failed
+        self.active &= ~(self.x[:, 4] > self.lengths - 0.1) & ~self.failed
         n_active = int(self.active.sum())
         if n_active == 0:
             return 0
         u = self.controller.command(self.x, active=self.active)
         self.failed |= self.active & (self.controller.info["status"] > 1)
         xn = self.x.clone()
-        e.plant_step(xn, u)
+        e.plant_step(xn, u, track_id=self.track_id)
         keep = (self.active & ~self.failed).unsqueeze(1)
         self.x = torch.where(keep, xn, self.x).contiguous()
         self.ticks += keep.squeeze(1).to(torch.int32)
