@@ -6,6 +6,7 @@ Workloads (BASELINE.json configs):
   nmpc     cascaded 20+35 NMPC with obstacles on ippodromo, one `command()`-equivalent batched solve per
            step from the warm start of the un-perturbed closed-loop tick (config C3; default once built)
   rollout  SingleTrack spatial RK4 rollout + [A|B] Jacobians, N=50 (config C5)
+  c2       cascaded 20+15, 4,096 perturbed instances: warm-started and cold-started solves (config C2)
 A "step" is one pass of the hot path over one batch.  `value` is device-resident throughput (CUDA events
 on the launch stream), `e2e` goes through the host-buffer C-ABI call with H2D/D2H inside the timed region.
 The instances shard across ranks with no data-path collective (weak scaling: per-GPU batch is fixed).
@@ -33,7 +34,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default=None, choices=["nmpc", "rollout"])
+    ap.add_argument("--workload", default=None, choices=["nmpc", "rollout", "c2"])
     ap.add_argument("--batch", type=int, default=0, help="instances per GPU (0 = config default)")
     ap.add_argument("--e2e-batch", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -54,6 +55,9 @@ def main():
     if workload == "rollout":
         from bench_rollout import run_rollout
         line = run_rollout(a, rank, world, local)
+    elif workload == "c2":
+        from bench_c2 import run_c2
+        line = run_c2(a, rank, world, local)
     else:
         from bench_nmpc import run_nmpc
         line = run_nmpc(a, rank, world, local)
