@@ -41,17 +41,23 @@ def _rollout_block(args):
     return x0.shape[0] * U.shape[1]
 
 
-def _nmpc_tasks(n):
+def _nmpc_tasks(n, c2=False):
     """n warm-started instances of the C3 workload: the reference run's warm ticks (fixture) with the bench's
-    perturbation recipe applied (seed 1003), obstacles on with the 7 ippodromo obstacles jittered."""
+    perturbation recipe applied (seed 1003), obstacles on with the 7 ippodromo obstacles jittered.
+    c2: the C2 workload instead (cascaded 20+15 of the run cascaded1_ippodromo, no obstacles, seed 1002)."""
     from bench_nmpc import controller_config
     from oracle.track import OracleTrack
-    cfg = controller_config()
     tr = OracleTrack(bc.load_yaml("environment/ippodromo.yaml"))
     z = np.load(os.path.join(bc.ROOT, "tests", "golden", "nmpc_oracle.npz"))
-    ticks = [t for t in ("cascaded3_ippodromo/cascaded/tick1", "cascaded3_ippodromo/cascaded/tick2")]
+    if c2:
+        with open(os.path.join(bc.ROOT, "tests", "golden", "runs.json")) as f:
+            cfg = dict(json.load(f)["cascaded1_ippodromo/cascaded"]["config"])
+        ticks = ["cascaded1_ippodromo/cascaded/tick1", "cascaded1_ippodromo/cascaded/tick2"]
+    else:
+        cfg = controller_config()
+        ticks = ["cascaded3_ippodromo/cascaded/tick1", "cascaded3_ippodromo/cascaded/tick2"]
     base = np.array([o[:3] for o in tr.obstacles], dtype=np.float64)
-    rng = np.random.default_rng(1003)
+    rng = np.random.default_rng(1002 if c2 else 1003)
     from oracle import nlp as on
     c = on.MpcCfg.from_config(cfg)
     tasks = []
@@ -93,9 +99,11 @@ def run_reference(a, workload):
             wl = "C5: SingleTrack trajectories x N=50 spatial RK4 + [A|B] (ippodromo)"
             sample = f"{procs} x {blk} trajectories x N=50 per step (oracle numpy RK4 + torch.func.jacfwd)"
         else:
-            cfg, tasks = _nmpc_tasks(procs)
+            cfg, tasks = _nmpc_tasks(procs, c2=workload == "c2")
             fn, unit, metric = _solve_tick, "solves/s", "NMPC solves/sec"
-            wl = "C3: cascaded NMPC 20+35 with obstacles, ippodromo, warm-started perturbed instances"
+            wl = ("C2: cascaded NMPC 20+15, ippodromo, 4,096 perturbed instances; warm start timed, cold start reported "
+                  "separately" if workload == "c2" else
+                  "C3: cascaded NMPC 20+35 with obstacles, ippodromo, warm-started perturbed instances")
             sample = (f"{procs} warm-started perturbed instances per step (one per worker, interior-point loop capped at 30 "
                       f"iterations and counted as solved), oracle/nlp.py + oracle/ipm.py; "
                       f"the reference's own logs report 14-25 solves/s for IPOPT+MA27 on 1 thread (BASELINE.md)")
