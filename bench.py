@@ -38,6 +38,9 @@ def parse():
     ap.add_argument("--batch", type=int, default=0, help="instances per GPU (0 = config default)")
     ap.add_argument("--e2e-batch", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-instances", type=int, default=0, help="instances per step of the CPU arm (0 = default sample)")
+    ap.add_argument("--scaling", default="strong", choices=["strong", "weak"],
+                    help="strong: the configuration's batch is split over the GPUs; weak: every GPU gets the whole batch")
     ap.add_argument("--lap-cache", default=None, help="npz file to save/load the untimed warm-start lap (profiling runs)")
     return ap.parse_args()
 

@@ -1,11 +1,17 @@
-"""bench.py --impl reference: the reference's CPU implementation of the hot path on the box's host cores.
+"""bench.py --impl reference, and the cpu_baseline leg: the reference's CPU path of the hot path on the box's host cores.
 
-CasADi / IPOPT are not installable offline, so the reference arm times the CPU restatement under
-oracle/ (numpy + torch-fp64 autodiff NLP and an IPOPT-style interior point: "kind": "port"), one single-threaded
-worker process per host core, on a BOUNDED sample of the same workload the B200 arm runs: each step solves one
-warm-started closed-loop tick of the C3 lap per worker (or, for the rollout workload, a block of trajectories per
-worker).  The warm-start material comes from the committed fixture tests/golden/nmpc_oracle.npz (ticks of the
-reference's own cascaded 20+35 run) so that no GPU is needed on this arm.
+CasADi / IPOPT are not installable offline and the reference is pure Python on top of them, so it cannot be
+compiled or run here.  The CPU arm is therefore the C++ fp64 restatement under oracle/cpp (kind "port-cpp": exact
+derivatives by second-order jets, IPOPT's published algorithm with second-order correction and inertia correction, a
+block-tridiagonal Bunch-Kaufman LDL^T in the role of MA27; g++ -O3, OpenMP over instances), with NO iteration cap
+(max_iter = IPOPT's default 3000), on all host threads, on a bounded sample of the very workload the B200 arm times:
+
+  nmpc / c2   a closed-loop lap is replayed on the CPU oracle from the reference's cold start (untimed, the protocol of
+              bench_nmpc.replay_lap), bench_nmpc.make_batch with the B200 arm's seed builds the 65,536 (4,096) perturbed
+              instances, and each step solves the first `--cpu-instances` (default 1,024) of them
+  rollout     each step rolls out the first 16,384 trajectories x N = 50 with first-order jets for the [A|B] blocks
+The reference's own logs give 14-25 solves/s for IPOPT+MA27 on one thread -- the restatement runs at a
+comparable per-thread rate, so the ratio against this arm is quotable.
 """
 from __future__ import annotations
 
@@ -18,107 +24,144 @@ import numpy as np
 import bench_common as bc
 
 
-def _solve_tick(args):
-    import torch
-    torch.set_num_threads(1)
-    from oracle import ipm, models as om, nlp as on
-    cfg, x0, kap, ds, obst, X0, U0 = args
+class OracleTrackView:
+    """what bench_nmpc.make_batch needs of a track, served by the oracle's track (no product code on this arm)"""
+    def __init__(self, tr):
+        self.tr, self.length = tr, tr.length
+
+    def obstacle_array(self):
+        return np.array([o[:3] for o in self.tr.obstacles], dtype=float)
+
+
+def oracle_lap(cfg, tr, max_ticks=2000, threads=0):
+    """Closed loop of ONE vehicle on the CPU oracle (racing.py:217-242 semantics; same protocol as bench_nmpc.replay_lap):
+    cold guess with the legacy MT19937 seed 31, un-shifted warm start, retry from the cold guess on a failure."""
+    from oracle import cpp_oracle as co, nlp as on
     c = on.MpcCfg.from_config(cfg)
-    p = on.NLP(c, om.DEFAULT, x0, kap, ds, obst if c.obstacles else None)
-    # bounded work per step: the interior-point loop is capped at 30 iterations (the B200 arm's median is 17, its
-    # p90 37); a capped solve still counts as one solve, which can only favour this CPU arm
-    r = ipm.solve(p, p.pack(X0, U0), ipm.IpmOptions(max_iter=30, max_restorations=0))
-    return 1
+    cc = co.mpc_config(c)
+    X0, U0 = on.cold_start(c, np.random.RandomState(31).random_sample((2, c.H)))
+    X, U = X0.copy(), U0.copy()
+    x = np.array([4.0, 0, 0, 0, 1.0, 0, 0, 0])
+    ob = np.array([o[:3] for o in tr.obstacles], dtype=float) if c.obstacles else None
+    rows = {"x0": [], "Xw": [], "Uw": [], "iters": [], "status": []}
+    for _ in range(max_ticks):
+        if x[4] > tr.length - 0.1:
+            break
+        rows["x0"].append(x.copy()); rows["Xw"].append(X.copy()); rows["Uw"].append(U.copy())
+        ds, kap = on.horizon_params(c, tr, x, X[0])
+        r = co.solve(cc, x, kap, ds, X, U, obstacles=ob, threads=1)
+        if int(r["status"]) > 1:
+            ds, kap = on.horizon_params(c, tr, x, X0[0])
+            r = co.solve(cc, x, kap, ds, X0, U0, obstacles=ob, threads=1)
+        rows["iters"].append(int(r["iters"])); rows["status"].append(int(r["status"]))
+        if rows["status"][-1] > 1:
+            break
+        X, U = r["X"], r["U"]
+        x = co.plant_step(x[None], U[None, :, 0], np.atleast_1d(tr.k(x[4])), 0.05)[0]
+    return {k: np.array(v) for k, v in rows.items()}
 
 
-def _rollout_block(args):
-    import torch
-    torch.set_num_threads(1)
-    from oracle import models as om
-    x0, U, kap, ds = args
-    X = om.st_rollout_spatial(om.DEFAULT, x0, U, kap, ds)
-    om.st_step_jac(om.DEFAULT, X[:, :-1].reshape(-1, 8), U.reshape(-1, 2), kap.reshape(-1), ds.reshape(-1))
-    return x0.shape[0] * U.shape[1]
-
-
-def _nmpc_tasks(n, c2=False):
-    """n warm-started instances of the C3 workload: the reference run's warm ticks (fixture) with the bench's
-    perturbation recipe applied (seed 1003), obstacles on with the 7 ippodromo obstacles jittered.
-    c2: the C2 workload instead (cascaded 20+15 of the run cascaded1_ippodromo, no obstacles, seed 1002)."""
-    from bench_nmpc import controller_config
-    from oracle.track import OracleTrack
-    tr = OracleTrack(bc.load_yaml("environment/ippodromo.yaml"))
-    z = np.load(os.path.join(bc.ROOT, "tests", "golden", "nmpc_oracle.npz"))
-    if c2:
-        with open(os.path.join(bc.ROOT, "tests", "golden", "runs.json")) as f:
-            cfg = dict(json.load(f)["cascaded1_ippodromo/cascaded"]["config"])
-        ticks = ["cascaded1_ippodromo/cascaded/tick1", "cascaded1_ippodromo/cascaded/tick2"]
-    else:
-        cfg = controller_config()
-        ticks = ["cascaded3_ippodromo/cascaded/tick1", "cascaded3_ippodromo/cascaded/tick2"]
-    base = np.array([o[:3] for o in tr.obstacles], dtype=np.float64)
-    rng = np.random.default_rng(1002 if c2 else 1003)
+def nmpc_sample(workload, n, lap=None):
+    """First n instances of the B200 arm's batch (same recipe, same seed); horizon parameters by the oracle's track."""
+    import bench_nmpc as bn
     from oracle import nlp as on
+    from oracle.track import OracleTrack
+    c2 = workload == "c2"
+    cfg = bn.controller_config(horizon_pm=15, obstacles=False) if c2 else bn.controller_config()
+    tr = OracleTrack(bc.load_yaml("environment/ippodromo.yaml"))
+    t0 = time.perf_counter()
+    if lap is None:
+        lap = oracle_lap(cfg, tr)
+    lap_s = time.perf_counter() - t0
+    B = 4096 if c2 else 65536
+    x0, Xw, Uw, ob, _ = bn.make_batch(lap, OracleTrackView(tr), B, 1002 if c2 else bn.SEED, cfg)
+    n = min(n, B)
     c = on.MpcCfg.from_config(cfg)
-    tasks = []
+    ds, kap = np.empty((n, c.H)), np.empty((n, c.H))
     for i in range(n):
-        t = ticks[i % len(ticks)]
-        x0 = z[t + "/x0"].copy()
-        x0[0] = max(x0[0] + rng.uniform(-.5, .5), 3.2)
-        x0[1] += rng.normal(0, .05); x0[2] += rng.normal(0, .02)
-        x0[3] = float(np.clip(x0[3] + rng.uniform(-.02, .02), -.4, .4))
-        x0[5] += rng.uniform(-.5, .5); x0[6] += rng.normal(0, .01); x0[7] = 0.0
-        ob = base.copy()
-        ob[:, 0] += rng.uniform(-1, 1, len(base)); ob[:, 1] += rng.uniform(-.3, .3, len(base))
-        X0, U0 = z[t + "/X"].copy(), z[t + "/U"].copy()   # previous solution, un-shifted (cascaded_mpc.py:320-321)
-        ds, kap = on.horizon_params(c, tr, x0, X0[0])
-        tasks.append((cfg, x0, kap, ds, ob, X0, U0))
-    return cfg, tasks
+        ds[i], kap[i] = on.horizon_params(c, tr, x0[i], Xw[i, 0])
+    return cfg, dict(x0=x0[:n], Xw=Xw[:n], Uw=Uw[:n], obst=None if ob is None else ob[:n], ds=ds, kappa=kap), lap_s, len(lap["x0"])
+
+
+def cpu_solve(cfg, s, threads=0):
+    from oracle import cpp_oracle as co
+    return co.solve(cfg, s["x0"], s["kappa"], s["ds"], s["Xw"], s["Uw"], obstacles=s["obst"], max_iter=3000, max_soc=4,
+                    threads=threads)
+
+
+def host_threads():
+    return max(1, len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1))
+
+
+def cpu_baseline_nmpc(cfg, sample, gpu_U=None, gpu_obj=None):
+    """cpu_baseline leg of the B200 arm: the same first instances of the batch the GPU just solved, on all host threads;
+    also reports how many of them the two arms agree on (controls and objective within 1e-6)."""
+    th = host_threads()
+    n = len(sample["x0"])
+    t0 = time.perf_counter()
+    r = cpu_solve(cfg, sample, th)
+    el = time.perf_counter() - t0
+    out = {"value": n / el, "unit": "solves/s", "cores": th, "kind": "port-cpp", "per_core": n / el / th,
+           "sample": f"first {n} instances of this batch solved by oracle/cpp (C++ restatement of CasADi AD + IPOPT, no iteration "
+                     f"cap, OpenMP over instances, {th} threads) in {el:.1f} s; mean {r['iters'].mean():.1f} iterations; "
+                     f"the reference's own logs: 14-25 solves/s per thread (IPOPT+MA27, BASELINE.md)",
+           "mean_iters": float(r["iters"].mean()), "converged_frac": float((r["status"] <= 1).mean())}
+    if gpu_U is not None:
+        rel = lambda a, b: np.abs(a - b) / np.maximum(1.0, np.abs(b))
+        eu = rel(gpu_U, r["U"]).reshape(n, -1).max(1)
+        eo = rel(gpu_obj, r["obj"])
+        same = (eu < 1e-6) & (eo < 1e-6)
+        out["parity"] = {"instances": n, "agree_1e-6": int(same.sum()), "frac": float(same.mean()),
+                         "max_rel_err_controls_of_agreeing": float(eu[same].max()) if same.any() else None,
+                         "note": "instances that disagree end in a different local solution of the non-convex NLP "
+                                 "(DESIGN.md section 2)"}
+    return out
 
 
 def run_reference(a, workload):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    import multiprocessing as mp
-    cores = max(1, len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1))
-    procs = min(cores, 64)
+    from oracle import cpp_oracle as co
+    th = host_threads()
     steps, warm = max(1, a.steps), max(0, a.warmup)
-    # one single-threaded worker per core: keep BLAS / OpenMP from oversubscribing the cores (inherited by the workers)
-    for v in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS", "NUMEXPR_NUM_THREADS"):
-        os.environ[v] = "1"
-    ctx = mp.get_context("spawn")
-    with ctx.Pool(procs) as pool:
-        if workload == "rollout":
-            from oracle.track import OracleTrack
-            tr = OracleTrack(bc.load_yaml("environment/ippodromo.yaml"))
-            blk = 256
-            mk = lambda i: bc.rollout_inputs(blk, 50, 1005 + i, tr, bc.golden_states())
-            tasks = [mk(i) for i in range(procs)]
-            fn, unit, metric = _rollout_block, "state-steps/s", "rollout+Jacobian state-steps/sec"
-            wl = "C5: SingleTrack trajectories x N=50 spatial RK4 + [A|B] (ippodromo)"
-            sample = f"{procs} x {blk} trajectories x N=50 per step (oracle numpy RK4 + torch.func.jacfwd)"
-        else:
-            cfg, tasks = _nmpc_tasks(procs, c2=workload == "c2")
-            fn, unit, metric = _solve_tick, "solves/s", "NMPC solves/sec"
-            wl = ("C2: cascaded NMPC 20+15, ippodromo, 4,096 perturbed instances; warm start timed, cold start reported "
-                  "separately" if workload == "c2" else
-                  "C3: cascaded NMPC 20+35 with obstacles, ippodromo, warm-started perturbed instances")
-            sample = (f"{procs} warm-started perturbed instances per step (one per worker, interior-point loop capped at 30 "
-                      f"iterations and counted as solved), oracle/nlp.py + oracle/ipm.py; "
-                      f"the reference's own logs report 14-25 solves/s for IPOPT+MA27 on 1 thread (BASELINE.md)")
-        for _ in range(min(warm, 1)):       # one warm-up pass is enough to page the workers in (each pass is ~30 s)
-            pool.map(fn, tasks)
-        done, t0 = 0, time.perf_counter()
-        for _ in range(steps):
-            done += sum(pool.map(fn, tasks))
-        el = time.perf_counter() - t0
-    value = done / el
+    extra = {}
+    if workload == "rollout":
+        from oracle.track import OracleTrack
+        tr = OracleTrack(bc.load_yaml("environment/ippodromo.yaml"))
+        nb = 16384
+        x0, U, kap, ds = bc.rollout_inputs(nb, 50, 1005, tr, bc.golden_states())
+        fn = lambda: co.rollout_st(x0, U, kap, ds, jac=True, threads=th)
+        units, unit, metric = nb * 50, "state-steps/s", "rollout+Jacobian state-steps/sec"
+        wl = "C5: 1M SingleTrack trajectories x N=50 spatial RK4 + [A|B] Jacobians (ippodromo)"
+        sample = f"{nb} trajectories x N=50 per step, oracle/cpp (RK4 in first-order jets), {th} threads"
+    else:
+        n = getattr(a, "cpu_instances", 0) or 1024
+        cfg, s, lap_s, ticks = nmpc_sample(workload, n)
+        n = len(s["x0"])
+        last = {}
+        def fn():
+            last["r"] = cpu_solve(cfg, s, th)
+        units, unit, metric = n, "solves/s", "NMPC solves/sec"
+        wl = ("C2: cascaded NMPC 20+15, ippodromo, 4,096 perturbed instances; warm start timed, cold start reported separately"
+              if workload == "c2" else "C3: cascaded NMPC 20+35 with obstacles, ippodromo, warm-started perturbed instances")
+        sample = (f"first {n} instances of the batch per step (same recipe and seed as the B200 arm; warm-start lap of {ticks} "
+                  f"ticks replayed on the CPU oracle in {lap_s:.0f} s, untimed), oracle/cpp with max_iter 3000, {th} threads")
+    for _ in range(min(warm, 1)):
+        fn()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        fn()
+    el = time.perf_counter() - t0
+    value = units * steps / el
+    if workload != "rollout":
+        r = last["r"]
+        extra = {"mean_iters": float(r["iters"].mean()), "max_iters": int(r["iters"].max()),
+                 "converged_frac": float((r["status"] <= 1).mean()), "per_core": value / th}
     line = {"impl": "reference", "metric": metric, "value": value, "unit": unit, "n_gpus": a.gpus, "steps": steps,
-            "warmup": warm, "ms_per_step": 1e3 * el / steps, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": {"workload": wl},
-            "gpu_launches": 0,
-            "cpu_baseline": {"value": value, "unit": unit, "cores": procs, "kind": "port", "sample": sample},
+            "warmup": warm, "ms_per_step": 1e3 * el / steps, "higher_is_better": True, "scaling": getattr(a, "scaling", "strong"),
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": {"workload": wl}, "gpu_launches": 0,
+            "cpu_baseline": dict({"value": value, "unit": unit, "cores": th, "kind": "port-cpp", "sample": sample}, **extra),
             "e2e": {"value": value, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
     return 0

@@ -1,6 +1,6 @@
 // ORACLE (test infrastructure only -- never linked into or loaded by the product path).
 //
-// Second-order forward-mode automatic differentiation on the host: a Jet<N> carries a value, its gradient with
+// Second-order forward-mode automatic differentiation on the host: a Jet<N, S> carries a value, its gradient with
 // respect to N stage variables and the packed lower triangle of its Hessian.  This plays the role CasADi's AD plays
 // in the reference (cascaded_mpc.py:65 "expand": True -> exact constraint Jacobian and Lagrangian Hessian for IPOPT).
 // It is deliberately a different mechanism from the product's hyper-dual (pair-per-thread) evaluation.
@@ -9,11 +9,11 @@
 
 namespace vco {
 
-template <int N> struct Jet {
-    static constexpr int NH = N * (N + 1) / 2;
+template <int N, bool SECOND = true> struct Jet {
+    static constexpr int NH = SECOND ? N * (N + 1) / 2 : 0;   // SECOND = false: gradient only (Jacobian sweeps)
     double v;
     double g[N];
-    double h[NH];   // h[i*(i+1)/2 + j], i >= j
+    double h[NH > 0 ? NH : 1];   // h[i*(i+1)/2 + j], i >= j
     Jet() {}
     Jet(double c) : v(c) { for (int i = 0; i < N; ++i) g[i] = 0.0; for (int i = 0; i < NH; ++i) h[i] = 0.0; }
     static Jet var(double x, int idx) { Jet r(x); r.g[idx] = 1.0; return r; }
@@ -21,87 +21,91 @@ template <int N> struct Jet {
 };
 
 inline double val(double x) { return x; }
-template <int N> inline double val(const Jet<N>& x) { return x.v; }
+template <int N, bool S> inline double val(const Jet<N, S>& x) { return x.v; }
 
 // chain rule for a univariate function with f, f', f'' known at x.v
-template <int N> inline Jet<N> lift(const Jet<N>& x, double f0, double f1, double f2) {
-    Jet<N> r;
+template <int N, bool S> inline Jet<N, S> lift(const Jet<N, S>& x, double f0, double f1, double f2) {
+    Jet<N, S> r;
     r.v = f0;
     for (int i = 0; i < N; ++i) r.g[i] = f1 * x.g[i];
-    int q = 0;
-    for (int i = 0; i < N; ++i) {
-        const double gi = f2 * x.g[i];
-        for (int j = 0; j <= i; ++j, ++q) r.h[q] = f1 * x.h[q] + gi * x.g[j];
+    if (S) {
+        int q = 0;
+        for (int i = 0; i < N; ++i) {
+            const double gi = f2 * x.g[i];
+            for (int j = 0; j <= i; ++j, ++q) r.h[q] = f1 * x.h[q] + gi * x.g[j];
+        }
     }
     return r;
 }
 
-template <int N> inline Jet<N> operator+(const Jet<N>& a, const Jet<N>& b) {
-    Jet<N> r; r.v = a.v + b.v;
+template <int N, bool S> inline Jet<N, S> operator+(const Jet<N, S>& a, const Jet<N, S>& b) {
+    Jet<N, S> r; r.v = a.v + b.v;
     for (int i = 0; i < N; ++i) r.g[i] = a.g[i] + b.g[i];
-    for (int i = 0; i < Jet<N>::NH; ++i) r.h[i] = a.h[i] + b.h[i];
+    for (int i = 0; i < Jet<N, S>::NH; ++i) r.h[i] = a.h[i] + b.h[i];
     return r;
 }
-template <int N> inline Jet<N> operator-(const Jet<N>& a, const Jet<N>& b) {
-    Jet<N> r; r.v = a.v - b.v;
+template <int N, bool S> inline Jet<N, S> operator-(const Jet<N, S>& a, const Jet<N, S>& b) {
+    Jet<N, S> r; r.v = a.v - b.v;
     for (int i = 0; i < N; ++i) r.g[i] = a.g[i] - b.g[i];
-    for (int i = 0; i < Jet<N>::NH; ++i) r.h[i] = a.h[i] - b.h[i];
+    for (int i = 0; i < Jet<N, S>::NH; ++i) r.h[i] = a.h[i] - b.h[i];
     return r;
 }
-template <int N> inline Jet<N> operator-(const Jet<N>& a) {
-    Jet<N> r; r.v = -a.v;
+template <int N, bool S> inline Jet<N, S> operator-(const Jet<N, S>& a) {
+    Jet<N, S> r; r.v = -a.v;
     for (int i = 0; i < N; ++i) r.g[i] = -a.g[i];
-    for (int i = 0; i < Jet<N>::NH; ++i) r.h[i] = -a.h[i];
+    for (int i = 0; i < Jet<N, S>::NH; ++i) r.h[i] = -a.h[i];
     return r;
 }
-template <int N> inline Jet<N> operator*(const Jet<N>& a, const Jet<N>& b) {
-    Jet<N> r; r.v = a.v * b.v;
+template <int N, bool S> inline Jet<N, S> operator*(const Jet<N, S>& a, const Jet<N, S>& b) {
+    Jet<N, S> r; r.v = a.v * b.v;
     for (int i = 0; i < N; ++i) r.g[i] = a.g[i] * b.v + a.v * b.g[i];
-    int q = 0;
-    for (int i = 0; i < N; ++i)
-        for (int j = 0; j <= i; ++j, ++q)
-            r.h[q] = a.h[q] * b.v + a.v * b.h[q] + a.g[i] * b.g[j] + a.g[j] * b.g[i];
+    if (S) {
+        int q = 0;
+        for (int i = 0; i < N; ++i)
+            for (int j = 0; j <= i; ++j, ++q)
+                r.h[q] = a.h[q] * b.v + a.v * b.h[q] + a.g[i] * b.g[j] + a.g[j] * b.g[i];
+    }
     return r;
 }
-template <int N> inline Jet<N> operator+(const Jet<N>& a, double c) { Jet<N> r = a; r.v += c; return r; }
-template <int N> inline Jet<N> operator+(double c, const Jet<N>& a) { Jet<N> r = a; r.v += c; return r; }
-template <int N> inline Jet<N> operator-(const Jet<N>& a, double c) { Jet<N> r = a; r.v -= c; return r; }
-template <int N> inline Jet<N> operator-(double c, const Jet<N>& a) { Jet<N> r = -a; r.v += c; return r; }
-template <int N> inline Jet<N> operator*(const Jet<N>& a, double c) {
-    Jet<N> r; r.v = a.v * c;
+template <int N, bool S> inline Jet<N, S> operator+(const Jet<N, S>& a, double c) { Jet<N, S> r = a; r.v += c; return r; }
+template <int N, bool S> inline Jet<N, S> operator+(double c, const Jet<N, S>& a) { Jet<N, S> r = a; r.v += c; return r; }
+template <int N, bool S> inline Jet<N, S> operator-(const Jet<N, S>& a, double c) { Jet<N, S> r = a; r.v -= c; return r; }
+template <int N, bool S> inline Jet<N, S> operator-(double c, const Jet<N, S>& a) { Jet<N, S> r = -a; r.v += c; return r; }
+template <int N, bool S> inline Jet<N, S> operator*(const Jet<N, S>& a, double c) {
+    Jet<N, S> r; r.v = a.v * c;
     for (int i = 0; i < N; ++i) r.g[i] = a.g[i] * c;
-    for (int i = 0; i < Jet<N>::NH; ++i) r.h[i] = a.h[i] * c;
+    for (int i = 0; i < Jet<N, S>::NH; ++i) r.h[i] = a.h[i] * c;
     return r;
 }
-template <int N> inline Jet<N> operator*(double c, const Jet<N>& a) { return a * c; }
-template <int N> inline Jet<N> inv(const Jet<N>& a) {
+template <int N, bool S> inline Jet<N, S> operator*(double c, const Jet<N, S>& a) { return a * c; }
+template <int N, bool S> inline Jet<N, S> inv(const Jet<N, S>& a) {
     const double r = 1.0 / a.v;
     return lift(a, r, -r * r, 2.0 * r * r * r);
 }
 inline double inv(double a) { return 1.0 / a; }
-template <int N> inline Jet<N> operator/(const Jet<N>& a, const Jet<N>& b) { return a * inv(b); }
-template <int N> inline Jet<N> operator/(const Jet<N>& a, double c) { return a * (1.0 / c); }
-template <int N> inline Jet<N> operator/(double c, const Jet<N>& b) { return inv(b) * c; }
+template <int N, bool S> inline Jet<N, S> operator/(const Jet<N, S>& a, const Jet<N, S>& b) { return a * inv(b); }
+template <int N, bool S> inline Jet<N, S> operator/(const Jet<N, S>& a, double c) { return a * (1.0 / c); }
+template <int N, bool S> inline Jet<N, S> operator/(double c, const Jet<N, S>& b) { return inv(b) * c; }
 
-template <int N> inline Jet<N> sqrt(const Jet<N>& a) {
+template <int N, bool S> inline Jet<N, S> sqrt(const Jet<N, S>& a) {
     const double s = std::sqrt(a.v);
     return lift(a, s, 0.5 / s, -0.25 / (s * a.v));
 }
-template <int N> inline Jet<N> sin(const Jet<N>& a) { const double s = std::sin(a.v), c = std::cos(a.v); return lift(a, s, c, -s); }
-template <int N> inline Jet<N> cos(const Jet<N>& a) { const double s = std::sin(a.v), c = std::cos(a.v); return lift(a, c, -s, -c); }
-template <int N> inline Jet<N> tan(const Jet<N>& a) {
+template <int N, bool S> inline Jet<N, S> sin(const Jet<N, S>& a) { const double s = std::sin(a.v), c = std::cos(a.v); return lift(a, s, c, -s); }
+template <int N, bool S> inline Jet<N, S> cos(const Jet<N, S>& a) { const double s = std::sin(a.v), c = std::cos(a.v); return lift(a, c, -s, -c); }
+template <int N, bool S> inline Jet<N, S> tan(const Jet<N, S>& a) {
     const double t = std::tan(a.v), d = 1.0 + t * t;
     return lift(a, t, d, 2.0 * t * d);
 }
-template <int N> inline Jet<N> atan(const Jet<N>& a) {
+template <int N, bool S> inline Jet<N, S> atan(const Jet<N, S>& a) {
     const double d = 1.0 / (1.0 + a.v * a.v);
     return lift(a, std::atan(a.v), d, -2.0 * a.v * d * d);
 }
-template <int N> inline Jet<N> tanh(const Jet<N>& a) {
+template <int N, bool S> inline Jet<N, S> tanh(const Jet<N, S>& a) {
     const double t = std::tanh(a.v), d = 1.0 - t * t;
     return lift(a, t, d, -2.0 * t * d);
 }
-template <int N> inline Jet<N> fabs(const Jet<N>& a) { return a.v < 0.0 ? -a : a; }
+template <int N, bool S> inline Jet<N, S> fabs(const Jet<N, S>& a) { return a.v < 0.0 ? -a : a; }
 using std::atan; using std::cos; using std::fabs; using std::sin; using std::sqrt; using std::tan; using std::tanh;
 
 }  // namespace vco

@@ -37,6 +37,7 @@ struct Options {          // extern "C" mirror: vco_options
     int max_restorations; // re-initialisations by rollout where IPOPT would enter restoration (substitute)
     int verbose;
     double obj_scale;     // > 0: fixed objective scaling (else gradient based at the initial point)
+    int watchdog;         // IPOPT watchdog_shortened_iter_trigger (default 10; 0 = off)
 };
 
 // IPOPT defaults (the reference sets none of them)
@@ -539,6 +540,13 @@ static Result solve_once(const Problem& P, std::vector<StageIt>& it, const Optio
         phi = sf * fv - mu * lns;
     };
 
+    // IPOPT's watchdog (IpBacktrackingLineSearch: StartWatchDog / StopWatchDog): after `watchdog` consecutive shortened
+    // steps the full step is taken for up to 3 iterations without asking the filter, the acceptance test being made
+    // against the stored reference point; if no acceptable point turns up, back to the stored iterate and backtrack
+    bool in_wd = false, skip_first = false;
+    int wd_short = 0, wd_trial = 0;
+    std::vector<StageIt> it_wd;
+    double theta_wd = 0, phi_wd = 0, dphi_wd = 0, atest_wd = 0;
     for (iter = 0; iter <= opt.max_iter; ++iter) {
         ok = eval_all(P, it, sf, f, ev);
         if (!ok) { status = ST_EVAL_ERROR; break; }
@@ -566,7 +574,7 @@ static Result solve_once(const Problem& P, std::vector<StageIt>& it, const Optio
         double trial = 0.0, alpha = 0.0, a_d = 1.0;
         bool accepted = false, failed = false;
         const std::vector<StageIt>* used = &d1;
-        auto acceptable = [&](double a_test, double tht, double pht, double dphi, bool& augment) {
+        auto acceptable_ref = [&](double a_test, double tht, double pht, double dphi, bool& augment, double theta, double phi) {
             augment = false;
             if (tht > theta_max) return false;
             for (auto& fe : filt) if (tht >= fe.first && pht >= fe.second) return false;
@@ -575,6 +583,11 @@ static Result solve_once(const Problem& P, std::vector<StageIt>& it, const Optio
             else if (tht <= (1 - GAMMA_THETA) * theta || pht <= phi - GAMMA_PHI * theta) { augment = true; return true; }
             return std::fabs(pht - phi) <= 1e-13 * std::fmax(1.0, std::fabs(phi)) && tht <= theta + 1e-13;
         };
+        auto acceptable = [&](double a_test, double tht, double pht, double dphi, bool& augment) {
+            return acceptable_ref(a_test, tht, pht, dphi, augment, theta, phi);
+        };
+        bool wd_restored = false;
+        int n_steps = 0;
         while (!accepted && !failed) {
             while (!kkt.factor(P, it, ev, trial)) {   // delta_w ladder
                 if (trial == 0.0) trial = first_ever ? 1e-4 : std::fmax(1e-20, delta_last / 3.0);
@@ -590,7 +603,26 @@ static Result solve_once(const Problem& P, std::vector<StageIt>& it, const Optio
                 for (int j = 0; j < P.ni(k); ++j) dphi -= mu * d1[k].s[j] / it[k].s[j];
             }
             alpha = a_p;
-            for (int bt = 0; bt < MAX_BACKTRACK && !accepted; ++bt, alpha *= 0.5) {
+            if (!in_wd && opt.watchdog > 0 && wd_short >= opt.watchdog && !skip_first && trial == 0.0) {
+                in_wd = true; it_wd = it; theta_wd = theta; phi_wd = phi; dphi_wd = dphi; atest_wd = a_p; wd_trial = 0;
+            }
+            if (in_wd) {
+                make_trial(d1, a_p);
+                double ft, tht = 0, pht = 0;
+                const bool okv = eval_values(P, tr, ft, evt);
+                bool augment = false, acc = false;
+                if (okv) { measures(tr, evt, ft, tht, pht); acc = acceptable_ref(atest_wd, tht, pht, dphi_wd, augment, theta_wd, phi_wd); }
+                if (acc) {
+                    in_wd = false; accepted = true; used = &d1; n_steps = 0;
+                    if (augment) filt.emplace_back((1 - GAMMA_THETA) * theta_wd, phi_wd - GAMMA_PHI * theta_wd);
+                } else if (!okv || ++wd_trial > 3) {
+                    it = it_wd; in_wd = false; wd_short = 0; skip_first = true; wd_restored = true;
+                } else { accepted = true; used = &d1; n_steps = 0; }   // full step taken on trust
+                break;
+            }
+            if (skip_first) alpha *= 0.5;
+            for (int bt = skip_first ? 1 : 0; bt < MAX_BACKTRACK && !accepted; ++bt, alpha *= 0.5) {
+                n_steps = bt;
                 make_trial(d1, alpha);
                 double ft, tht = 0, pht = 0;
                 const bool okv = eval_values(P, tr, ft, evt);
@@ -615,7 +647,7 @@ static Result solve_once(const Problem& P, std::vector<StageIt>& it, const Optio
                         if (!ok2) break;
                         measures(tr, evt, ft2, tht2, pht2);
                         if (acceptable(alpha, tht2, pht2, dphi, augment)) {
-                            accepted = true; used = &d2; alpha = a_p2; a_d = a_d2;
+                            accepted = true; used = &d2; alpha = a_p2; a_d = a_d2; n_steps = 0;
                             break;
                         }
                         if (tht2 > KAPPA_SOC * theta_soc_old) break;
@@ -636,8 +668,11 @@ static Result solve_once(const Problem& P, std::vector<StageIt>& it, const Optio
             trial = std::fmax(trial, 1e-4) * 100.0;
             if (trial > 1e12) failed = true;
         }
+        if (wd_restored) { --iter; continue; }   // back at the stored iterate: the regular line search follows
+        skip_first = false;
         if (failed || !accepted) { status = ST_LINESEARCH_FAIL; break; }
         if (trial > 0) delta_last = trial;
+        wd_short = n_steps == 0 ? 0 : wd_short + 1;
         if (opt.verbose) std::fprintf(stderr, "      alpha %.3e a_d %.3e delta_w %.2e soc %d\n", alpha, a_d, trial, used == &d2);
         const std::vector<StageIt>& d = *used;
         for (int k = 0; k < H; ++k) {
@@ -680,7 +715,7 @@ static Result solve(const Problem& P, std::vector<StageIt>& it, const Options& o
 // ------------------------------------------------------------------------------------------------ C interface
 extern "C" {
 
-typedef struct vco_options { int max_iter, max_soc, max_restorations, verbose; double obj_scale; } vco_options;
+typedef struct vco_options { int max_iter, max_soc, max_restorations, verbose; double obj_scale; int watchdog; } vco_options;
 
 int vco_version(void) { return 2; }
 int vco_num_threads(void) {
@@ -699,7 +734,8 @@ int vco_nmpc_solve(const vc_model_params* par, const vc_mpc_config* cfg, const v
     using namespace vco;
     const int N = cfg->N, M = cfg->M, H = N + M;
     if (H < 1 || H > 4096) return -1;
-    Options opt{o ? o->max_iter : 3000, o ? o->max_soc : 4, o ? o->max_restorations : 2, o ? o->verbose : 0, o ? o->obj_scale : 0.0};
+    Options opt{o ? o->max_iter : 3000, o ? o->max_soc : 4, o ? o->max_restorations : 2, o ? o->verbose : 0, o ? o->obj_scale : 0.0,
+                o ? o->watchdog : 10};
 #ifdef _OPENMP
     if (n_threads > 0) omp_set_num_threads(n_threads);
 #pragma omp parallel for schedule(dynamic, 1)
@@ -777,7 +813,7 @@ int vco_rollout_st(const vc_model_params* par, int B, int N, const double* x0, c
             const double* u = U + ((size_t)b * N + n) * 2;
             const double k = kappa[(size_t)b * N + n], h = ds[(size_t)b * N + n];
             if (AB) {
-                typedef Jet<10> J;   // (second-order parts are computed and dropped: this is the oracle, not the fast path)
+                typedef Jet<10, false> J;   // first-order jets: value + the 10 columns of [A|B]
                 J y[10], xn[8];
                 for (int i = 0; i < 8; ++i) y[i] = J::var(Xb[n * 8 + i], i);
                 y[8] = J::var(u[0], 8); y[9] = J::var(u[1], 9);

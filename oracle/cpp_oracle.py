@@ -43,7 +43,7 @@ MpcConfig = _struct_from_header("vc_mpc_config")
 
 class Options(C.Structure):
     _fields_ = [("max_iter", C.c_int), ("max_soc", C.c_int), ("max_restorations", C.c_int), ("verbose", C.c_int),
-                ("obj_scale", C.c_double)]
+                ("obj_scale", C.c_double), ("watchdog", C.c_int)]
 
 
 def build(force: bool = False) -> str:
@@ -116,7 +116,7 @@ def _a(x, dtype=np.float64):
 
 
 def solve(cfg, x0, kappa, ds, X, U, obstacles=None, car=None, max_iter=3000, max_soc=4, max_restorations=2, verbose=0,
-          threads=0, obj_scale=0.0):
+          threads=0, obj_scale=0.0, watchdog=0):
     """Batched solve on the host cores.  x0[B,8], kappa[B,H], ds[B,H], X[B,8,H], U[B,2,H] (warm start), obstacles[B,n,3].
     Returns dict(X, U, obj, status, iters, kkt) of new arrays."""
     lib = load()
@@ -138,7 +138,7 @@ def solve(cfg, x0, kappa, ds, X, U, obstacles=None, car=None, max_iter=3000, max
         assert ob.shape == (B, n_obs, 3)
     obj, kkt = np.empty(B), np.empty(B)
     status, iters = np.empty(B, np.int32), np.empty(B, np.int32)
-    o = Options(int(max_iter), int(max_soc), int(max_restorations), int(verbose), float(obj_scale))
+    o = Options(int(max_iter), int(max_soc), int(max_restorations), int(verbose), float(obj_scale), int(watchdog))
     rc = lib.vco_nmpc_solve(C.byref(p), C.byref(c), C.byref(o), B, x0.ctypes.data, kappa.ctypes.data, ds.ctypes.data,
                             ob.ctypes.data if ob is not None else None, n_obs, X.ctypes.data, U.ctypes.data, obj.ctypes.data,
                             status.ctypes.data, iters.ctypes.data, kkt.ctypes.data, int(threads))

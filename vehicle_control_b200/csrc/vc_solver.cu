@@ -17,9 +17,11 @@
 #include <cstdlib>
 #include <vector>
 #include "vc_handle.h"
-#include "vc_nlp.cuh"
+#include "vc_adj.cuh"
 
 namespace vc {
+
+#define FULL_MASK 0xffffffffu
 
 // ------------------------------------------------------------------------------------------------
 // per-instance workspace (global memory): one contiguous slab per instance made of H stage RECORDS of
@@ -178,92 +180,101 @@ __global__ void k_prepare(Prob pr, Ws ws, int* list0, int* count0) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// k_eval_st: one thread per (instance, SingleTrack stage, pair (a,b) of active variables).  The stage's
-// Lagrangian terms are evaluated once in hyper-dual arithmetic seeded along (a,b): values, d/da, d/db, d2/dadb.
+// k_eval_st: eight threads per (instance, SingleTrack stage), one per active variable a.  Each runs the stage functions
+// forward in Dual1 arithmetic seeded along a (column a of the dynamics / inequality Jacobians) and the hand-written
+// adjoint sweep of vc_adj.cuh in the same arithmetic (gradient of the stage Lagrangian + column a of its exact Hessian);
+// the Gauss-Newton part Jc^T (z/s) Jc is assembled from the eight Jacobian columns with warp shuffles.
 #ifndef VC_EVAL_MINBLOCKS
 #define VC_EVAL_MINBLOCKS 1
 #endif
+constexpr int EVAL_ST_LANES = 8;
 __global__ void __launch_bounds__(128, VC_EVAL_MINBLOCKS) k_eval_st(Prob pr, Ws ws) {
     const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const int N = pr.N;
-    if (t >= (long long)(*pr.act_count) * N * 36) return;
-    const int q = (int)(t % 36), k = (int)((t / 36) % N), b = pr.act_list[(int)(t / (36LL * N))];
-    const double* sc = ws.scal(b);
-    int ia, ib;
-    pair_from_index(q, ia, ib);
-    const int va = c_act_st[ia], vb = c_act_st[ib];
-    const bool diag = ia == ib;
+    const bool live = t < (long long)(*pr.act_count) * N * EVAL_ST_LANES;
+    const unsigned mask = __ballot_sync(FULL_MASK, live);   // groups of 8 lanes enter or leave together
+    if (!live) return;
+    const int ia = (int)(t % EVAL_ST_LANES), k = (int)((t / EVAL_ST_LANES) % N), b = pr.act_list[(int)(t / ((long long)EVAL_ST_LANES * N))];
+    const int va = c_act_st[ia];
     const double* yv = ws.at(b, W_Y, k);
-    HDual y[10];
+    Dual1 y[10];
 #pragma unroll
-    for (int i = 0; i < 10; ++i) y[i] = HDual{yv[i], i == va ? 1.0 : 0.0, i == vb ? 1.0 : 0.0, 0.0};
-    const double sf = sc[S_SF];
+    for (int i = 0; i < 10; ++i) y[i] = Dual1{yv[i], i == va ? 1.0 : 0.0};
+    const double sf = ws.scal(b)[S_SF];
     const double kap = pr.kappa[(size_t)b * pr.H + k], ds = pr.ds[(size_t)b * pr.H + k];
     const bool last_st = k == N - 1;
-    HDual cost, ineq[NI_ST];
-    st_cost_ineq(pr.p, pr.c, y, ds, last_st && pr.M == 0, cost, ineq);
-    const double *z = ws.at(b, W_Z, k), *s = ws.at(b, W_S, k);
-    double hab = sf * cost.ab, ga = sf * cost.a, rda, v1 = 0.0, v2 = 0.0;
-    rda = ga;
+    const int mode = !last_st ? 0 : (pr.M > 0 ? 2 : 1);
+    double z[NI_ST], sg[NI_ST], lam[8];
+    {
+        const double *zz = ws.at(b, W_Z, k), *ss = ws.at(b, W_S, k);
+#pragma unroll
+        for (int j = 0; j < NI_ST; ++j) { z[j] = zz[j]; sg[j] = 1.0 / ss[j]; }
+    }
+    const double* yn = mode != 1 ? ws.at(b, W_Y, k + 1) : nullptr;
+    if (mode != 1) {
+        const double* ln = ws.at(b, W_LAM, k + 1);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) lam[i] = (mode == 0 || i < 5) ? ln[i] : 0.0;
+    }
+    Dual1 cost, ineq[NI_ST], xn[8];
+    InAdj<Dual1> g;
+    double kT = 0.0;
+    st_stage_for<Dual1>(pr.p, pr.c, y, kap, ds, mode, sf, z, lam, mode == 2 ? -2.0 * (sf * pr.c.w_switch_F / ds) : 0.0,
+                        mode == 2 ? yn[QFY] : 0.0, cost, ineq, xn, g, &kT);
+    // ---- column a of the Jacobians, gradients
+    double* ab = ws.at(b, W_AB, k);
     double* jc = ws.at(b, W_JC, k);
+    double v1 = 0.0, v2 = 0.0, ga = sf * cost.d;
 #pragma unroll
     for (int j = 0; j < NI_ST; ++j) {
-        const double zj = z[j], is = 1.0 / s[j];
-        hab += -zj * ineq[j].ab + zj * is * ineq[j].a * ineq[j].b;
-        rda -= zj * ineq[j].a;
-        v1 += ineq[j].a * is;
-        v2 += ineq[j].a * zj * ineq[j].v * is;
-        if (diag) jc[j * 8 + ia] = ineq[j].a;
+        jc[j * 8 + ia] = ineq[j].d;
+        v1 += ineq[j].d * sg[j];
+        v2 += ineq[j].d * z[j] * ineq[j].v * sg[j];
     }
-    double* ab = ws.at(b, W_AB, k);
-    if (!last_st) {
-        HDual xn[8];
-        st_rk4<true>(pr.p, y, y + 8, kap, ds, xn);
-        const double* lam = ws.at(b, W_LAM, k + 1);
-        const double* yn = ws.at(b, W_Y, k + 1);
-        double* gres = ws.at(b, W_GRES, k + 1);
+    if (mode == 0) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            hab -= lam[i] * xn[i].ab;
-            rda -= lam[i] * xn[i].a;
-            if (diag) ab[i * 8 + ia] = xn[i].a;
-            if (q == 0) gres[i] = yn[i] - xn[i].v;
-        }
-    } else if (pr.M > 0) {
-        HDual xp[5], T;
-        st_switch(pr.p, y, xp, T);
-        const double* lam = ws.at(b, W_LAM, k + 1);
-        const double* yn = ws.at(b, W_Y, k + 1);
-        double* gres = ws.at(b, W_GRES, k + 1);
+        for (int i = 0; i < 8; ++i) ab[i * 8 + ia] = xn[i].d;
+    } else if (mode == 2) {
 #pragma unroll
-        for (int i = 0; i < 5; ++i) {
-            hab -= lam[i] * xp[i].ab;
-            rda -= lam[i] * xp[i].a;
-            if (diag) ab[i * 8 + ia] = xp[i].a;
-            if (q == 0) gres[i] = yn[i] - xp[i].v;
-        }
-        // switching cost sf*W/ds*(Fy_N - T(y))^2: curvature and gradient w.r.t. this stage (its Gauss-Newton
-        // part enters the Riccati recursion through the lifted variable, see k_step)
-        const double kT = -2.0 * (sf * pr.c.w_switch_F / ds) * (yn[QFY] - T.v);
-        hab += kT * T.ab;
-        rda += kT * T.a;
-        ga += kT * T.a;
-        if (diag) ab[5 * 8 + ia] = T.a;
-        if (q == 0) ab[6 * 8] = T.v;
+        for (int i = 0; i < 6; ++i) ab[i * 8 + ia] = xn[i].d;   // rows 0..4: PointMass state, row 5: grad T
+        ga += kT * xn[5].d;
     }
-    if (diag && va < 8) rda += ws.at(b, W_LAM, k)[va];
-    ws.at(b, W_HC, k)[q] = hab;
-    if (diag) {
-        ws.at(b, W_RD, k)[va] = rda;
-        ws.at(b, W_GF, k)[va] = ga;
-        ws.at(b, W_V1, k)[va] = v1;
-        ws.at(b, W_V2, k)[va] = v2;
+    const Dual1 gg[8] = {g.Ux, g.Uy, g.r, g.delta, g.ey, g.epsi, g.Fx, g.w};
+    double rda = 0.0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) if (i == ia) rda = gg[i].v;
+    if (va < 8) rda += ws.at(b, W_LAM, k)[va];
+    ws.at(b, W_RD, k)[va] = rda;
+    ws.at(b, W_GF, k)[va] = ga;
+    ws.at(b, W_V1, k)[va] = v1;
+    ws.at(b, W_V2, k)[va] = v2;
+    // ---- Hessian column a: exact Lagrangian part from the adjoint sweep + Gauss-Newton part of the barrier term
+    double hcol[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) hcol[i] = gg[i].d;
+    const int base = (threadIdx.x & 31) & ~(EVAL_ST_LANES - 1);
+    __syncwarp(mask);
+#pragma unroll
+    for (int j = 0; j < NI_ST; ++j) {
+        const double w = z[j] * sg[j] * ineq[j].d;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) hcol[i] += w * __shfl_sync(mask, ineq[j].d, base + i);
     }
-    if (q == 0) {
+    double* hc = ws.at(b, W_HC, k);
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+        if (i >= ia) hc[i * (i + 1) / 2 + ia] = hcol[i];
+    if (ia == 0) {
         double* cres = ws.at(b, W_CRES, k);
 #pragma unroll
         for (int j = 0; j < NI_ST; ++j) cres[j] = ineq[j].v;
         ws.at(b, W_FST, k)[0] = cost.v;
+        if (mode != 1) {
+            double* gres = ws.at(b, W_GRES, k + 1);
+            const int nn = mode == 0 ? 8 : 5;
+            for (int i = 0; i < nn; ++i) gres[i] = yn[i] - xn[i].v;
+            if (mode == 2) ab[6 * 8] = xn[5].v;
+        }
         if (k == 0) {
             double* g0 = ws.at(b, W_GRES, 0);
             for (int i = 0; i < 8; ++i) g0[i] = yv[i] - pr.x0[(size_t)b * 8 + i];
@@ -1770,7 +1781,7 @@ int launch_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_k
     };
     for (; pass < max_pass; ++pass) {
         // grids are sized by the last count read back (an upper bound); the kernels read the exact count on the device
-        const long long t_st = (long long)n_act * pr.N * 36, t_pm = (long long)n_act * pr.M * 15;
+        const long long t_st = (long long)n_act * pr.N * EVAL_ST_LANES, t_pm = (long long)n_act * pr.M * 15;
         pr.act_list = lists[cur]; pr.act_count = counts[cur];
         if (prof) h->prof_instance_passes += n_act;
         mark();
