@@ -8,8 +8,10 @@
  *   - every pointer argument named d_* is a DEVICE pointer to contiguous row-major memory owned by
  *     the caller (fp64 unless stated int32); h_* are host pointers, copied during the call.
  *   - all functions return 0 on success, <0 on error; vc_last_error() gives a thread-local message.
- *   - work is enqueued on the handle's CUDA stream; no hidden device synchronisation except where
- *     stated.  A handle is bound to one device and is not re-entrant.
+ *   - work is enqueued on the handle's CUDA stream.  The rollout / track / plant entry points are asynchronous;
+ *     vc_nmpc_solve is NOT: its interior-point loop reads the number of unfinished instances back once per pass
+ *     (a 4-byte copy + stream synchronisation) to size the next launches, so it returns with the results complete.
+ *     A handle is bound to one device and is not re-entrant.
  *   - state order  SingleTrack: Ux Uy r delta s ey epsi t   (models/dynamic_car.py:246-247)
  *                  PointMass  : V s ey epsi t              (models/dynamic_point_mass.py:155-156)
  *     input order  SingleTrack: Fx w ; PointMass: Fx Fy     (dynamic_car.py:208-209, dynamic_point_mass.py:120-121)
@@ -52,7 +54,19 @@ typedef struct vc_mpc_config {
     double mu_init;            /* 0.1                                                           */
     double bound_relax;        /* 1e-8                                                          */
     int warm_rungs;            /* >0: the first iteration starts this many rungs down the barrier ladder (warm starts) */
-    int reserved0;
+    int max_soc;               /* IPOPT max_soc: second-order correction steps per iteration (default 4)             */
+    /* engine policies that stand in for IPOPT mechanisms this engine does not restate (watchdog, restoration phase);
+     * vc_default_config() sets the values the shipped results were produced with */
+    int stall_iters;           /* consecutive shortened steps before the barrier parameter is forced down (4)        */
+    int restore_iters;         /* consecutive shortened steps at an infeasible iterate before it is projected onto the
+                                  dynamics (8; 0 = never)                                                            */
+    int max_damp;              /* damped re-solves of one iteration's direction before giving the direction up (8)   */
+    int giveup_iters;          /* shortened steps after the last projection before the instance ends with
+                                  VC_LINESEARCH_FAIL (24)                                                            */
+    int restore_check;         /* 1: a projected trajectory that leaves the widened state bounds is replaced by the
+                                  neutral rollout                                                                    */
+    int wide_max;              /* passes with at most this many unfinished instances run one BLOCK per instance
+                                  (latency) instead of one warp (throughput); 0 = never (296 = two per SM)           */
 } vc_mpc_config;
 
 typedef struct vc_handle vc_handle;
@@ -69,6 +83,9 @@ int vc_create(const vc_model_params* h_params, const vc_mpc_config* h_cfg, int d
               vc_handle** out);
 int vc_destroy(vc_handle* h);
 int vc_set_config(vc_handle* h, const vc_mpc_config* h_cfg);
+/* fills the solver options of *cfg (tol .. wide_max, max_iter) with the defaults: IPOPT's as the reference leaves them
+ * (cascaded_mpc.py:55-65) and this engine's policies; the controller part (N .. ey_max_pm) is left untouched */
+int vc_default_config(vc_mpc_config* h_cfg);
 
 /* replaces: Track._precompute_curvatures / Track.k (environment/track.py:156-167) and the x/y
  * splines behind rel2glob (track.py:102-129,206-252).  Cubic not-a-knot B-spline COEFFICIENTS built

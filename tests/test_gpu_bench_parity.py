@@ -62,6 +62,7 @@ def test_bench_instances_match_oracle(workload, n_min):
     print(f"{workload}: {n} bench instances, max |dU| {eu.max():.2e} |dX| {ex.max():.2e} dObj {eo.max():.2e}; "
           f"iterations equal to the oracle's on {same_it}/{n} (engine mean {it.mean():.1f}, oracle {f['iters'].mean():.1f})")
     assert eu.max() < TOL and ex.max() < TOL and eo.max() < TOL
+    assert same_it >= 0.6 * n      # same algorithm: most instances take the very same number of iterations
     # the instances the Python oracle solved as well (independent derivatives + dense LDL^T)
     py = ~np.isnan(f["U_py"]).reshape(n, -1).any(1)
     assert py.sum() >= 2 and _rel(Ug[py], f["U_py"][py]).max() < TOL
@@ -93,3 +94,21 @@ def test_fixture_is_drawn_from_the_bench_batch():
     base = tr.obstacle_array()
     assert np.abs(f["obst"][:, :, 2] - base[None, :, 2]).max() == 0.0     # radii are not jittered
     assert np.abs(f["obst"][:, :, 0] - base[None, :, 0]).max() <= 1.0 and np.abs(f["obst"][:, :, 1] - base[None, :, 1]).max() <= 0.3
+
+
+def test_block_wide_kernels_equal_warp_kernels_bit_for_bit():
+    """The late-pass kernels (one block per instance: k_step_a_wide / k_step_b_wide) compute every number with the same
+    arithmetic as the warp-per-instance kernels: the 64 C3 bench instances solved entirely by one or the other path
+    (wide_max = 0 / large) return identical bits -- so a result does not depend on how many instances share its batch."""
+    import torch
+    f = _fx("c3")
+    res = []
+    for wide_max in (0, 1 << 20):
+        eng, cfg = _engine("c3")
+        eng.set_config(cfg, wide_max=wide_max)
+        x0, X, U = eng.tensor(f["x0"]), eng.tensor(f["Xw"]), eng.tensor(f["Uw"])
+        ds, kap = eng.horizon_params(x0, X)
+        out = eng.solve(x0, kap, ds, X, U, obstacles=eng.tensor(f["obst"]))
+        res.append((X.clone(), U.clone(), out["obj"].clone(), out["iters"].clone(), out["status"].clone()))
+    for a, b in zip(*res):
+        assert torch.equal(a, b)

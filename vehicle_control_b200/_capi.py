@@ -30,7 +30,8 @@ class MpcConfig(C.Structure):
                                     "ey_min", "ey_max", "V_min", "ey_min_pm", "ey_max_pm",
                                     "tol", "acceptable_tol")]
                 + [("acceptable_iter", C.c_int), ("obj_scaling", C.c_int), ("mu_init", D), ("bound_relax", D),
-                   ("warm_rungs", C.c_int), ("reserved0", C.c_int)])
+                   ("warm_rungs", C.c_int), ("max_soc", C.c_int), ("stall_iters", C.c_int), ("restore_iters", C.c_int),
+                   ("max_damp", C.c_int), ("giveup_iters", C.c_int), ("restore_check", C.c_int), ("wide_max", C.c_int)])
 
 
 EXPORTS = {
@@ -40,6 +41,7 @@ EXPORTS = {
     "vc_create": (C.c_int, [C.POINTER(ModelParams), C.POINTER(MpcConfig), C.c_int, C.c_void_p, C.POINTER(C.c_void_p)]),
     "vc_destroy": (C.c_int, [C.c_void_p]),
     "vc_set_config": (C.c_int, [C.c_void_p, C.POINTER(MpcConfig)]),
+    "vc_default_config": (C.c_int, [C.POINTER(MpcConfig)]),
     "vc_set_track": (C.c_int, [C.c_void_p, PD, C.c_int, D, D, PD, PD, C.c_int, D]),
     "vc_track_curvature": (C.c_int, [C.c_void_p, C.c_int, PD, PD]),
     "vc_rel2glob": (C.c_int, [C.c_void_p, C.c_int, PD, PD, PD, PD]),

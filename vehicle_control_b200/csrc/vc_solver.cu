@@ -35,6 +35,7 @@ enum WsArray {
     W_V1,        // [10] Jc^T (1/s)
     W_V2,        // [10] Jc^T (z c / s)
     W_OBS,       // [8]  obstacle term: value, d/ds, d/dey, ss, s-ey, ey-ey; [6],[7] = slew weights tying u_k to u_{k-1}
+    W_AUX,       // [2]  Riccati pre-pass: direction of s at this stage; cost-to-go gradient of t of the NEXT stage
     W_GRES,      // [8]  equality residual of the row block that defines x_k
     W_KM,        // [24] feedback gains K[2][10], kff[2]
     W_PV,        // [10] Riccati cost-to-go gradient
@@ -65,7 +66,7 @@ enum WsArray {
 struct WsTable { int width[W_COUNT + 1]; int off[W_COUNT + 1]; };
 constexpr WsTable make_ws_table() {
     WsTable t{};
-    const int w[W_COUNT] = {36, 80, 10, 10, 10, 8, 8, 24, 10, 100, 10, 8, 10, 10, 80, 10, 10, 1, 1,
+    const int w[W_COUNT] = {36, 80, 10, 10, 10, 8, 2, 8, 24, 10, 100, 10, 8, 10, 10, 80, 10, 10, 1, 1,
                             10, 8, 10, 10, 8, 10, 8, 10, 10, 8, 10, 10};
     int o = 0;
     for (int i = 0; i < W_COUNT; ++i) { t.width[i] = w[i]; t.off[i] = o; o += w[i]; }
@@ -79,7 +80,7 @@ __device__ __constant__ int c_ws_off[W_COUNT + 1] = {
     WS_TABLE.off[13], WS_TABLE.off[14], WS_TABLE.off[15], WS_TABLE.off[16], WS_TABLE.off[17], WS_TABLE.off[18],
     WS_TABLE.off[19], WS_TABLE.off[20], WS_TABLE.off[21], WS_TABLE.off[22], WS_TABLE.off[23], WS_TABLE.off[24],
     WS_TABLE.off[25], WS_TABLE.off[26], WS_TABLE.off[27], WS_TABLE.off[28], WS_TABLE.off[29], WS_TABLE.off[30],
-    WS_TABLE.off[31]};
+    WS_TABLE.off[31], WS_TABLE.off[32]};
 constexpr int ws_width(int a) { return WS_TABLE.width[a]; }
 constexpr int ws_offset(int a) { return WS_TABLE.off[a]; }   // offset inside a stage record
 constexpr int WS_PER_STAGE = ws_offset(W_COUNT);
@@ -88,13 +89,18 @@ constexpr int WS_FWD0 = ws_offset(W_GRES);    // forward sweep: AB block and [WS
 constexpr int WS_FWD1 = ws_offset(W_Y);
 static_assert(WS_PER_STAGE % 2 == 0 && WS_BWD % 2 == 0 && WS_FWD0 % 2 == 0 && WS_FWD1 % 2 == 0 &&
               ws_offset(W_AB) % 2 == 0 && ws_offset(W_RD) % 2 == 0, "16-byte alignment of the staged blocks");
-static_assert(W_COUNT == 31, "update make_ws_table / c_ws_off");
+static_assert(W_COUNT == 32, "update make_ws_table / c_ws_off");
 constexpr int O_IT = ws_offset(W_Y), O_DIR = ws_offset(W_DY), O_DIR2 = ws_offset(W_DY2);
 static_assert(ws_offset(W_LAM) == O_IT + 10 && ws_offset(W_S) == O_IT + 18 && ws_offset(W_Z) == O_IT + 28 &&
               ws_offset(W_DLAM) == O_DIR + 10 && ws_offset(W_DSL) == O_DIR + 18 && ws_offset(W_DZ) == O_DIR + 28 &&
               ws_offset(W_DLAM2) == O_DIR2 + 10 && ws_offset(W_DSL2) == O_DIR2 + 18 && ws_offset(W_DZ2) == O_DIR2 + 28,
               "iterate / direction blocks must share one layout");
 constexpr int NSCAL = 96;
+#ifdef VC_TIMING
+#define VC_TICK(slot) do { if (rank_for_tick == 0) ws.scal(b)[84 + (slot)] = (double)clock64(); } while (0)
+#else
+#define VC_TICK(slot) do { } while (0)
+#endif
 // scalar block of an instance
 enum Scal { S_MU = 0, S_SF, S_DELTA_LAST, S_THETA0, S_NFILT, S_ACC, S_MODE, S_RESTARTS, S_OBJ, S_ERR, S_ITERS,
             S_STATUS, S_DBG_ALPHA, S_DBG_AP, S_DBG_THETA, S_DBG_DPHI, S_FILT = 16, S_NREST = 48, S_DBG_NAN = 50, S_DBG_THT0, S_DBG_PHT0, S_DBG_PHI, S_DBG_SOC, S_DBG_THT2, S_DBG_AP2, S_SHORT /* theta[16] */, S_FILP = 32 /* phi[16] */ };
@@ -131,8 +137,6 @@ struct Prob {   // device-side view of one vc_nmpc_solve call
     int max_damp;      // damped re-solves of one iteration's direction before the iterate is restored / given up
     int giveup_iters;  // consecutive shortened steps after the last restoration before the instance is given up
     int restore_iters; // > 0: consecutive shortened steps before the iterate is projected onto the dynamics (restoration)
-    double z_cap;      // > 0: initial multipliers min(mu/s, z_cap)
-    double z_init;   // > 0: constant initial inequality multipliers (IPOPT warm_start_mult_bound_push); else mu/s
     const double *x0, *kappa, *ds, *obst;
     double *X, *U, *obj, *kkt;
     int *status, *iters;
@@ -572,7 +576,7 @@ __device__ void init_slacks(const Prob& pr, const Ws& ws, int b, int lane, doubl
         double *s = ws.at(b, W_S, k), *z = ws.at(b, W_Z, k), *lam = ws.at(b, W_LAM, k);
         for (int j = 0; j < (k < pr.N ? NI_ST : NI_PM); ++j) {
             s[j] = fmax(cr[j], IpmConst::slack_push * fmax(1.0, fabs(cr[j])));
-            z[j] = pr.z_init > 0.0 ? pr.z_init : (pr.z_cap > 0.0 ? fmin(mu / s[j], pr.z_cap) : mu / s[j]);
+            z[j] = mu / s[j];
         }
         for (int i = 0; i < 8; ++i) lam[i] = 0.0;
     }
@@ -616,53 +620,75 @@ template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile(
 
 // offsets inside a stage record / inside the staged copies
 constexpr int O_HC = ws_offset(W_HC), O_AB = ws_offset(W_AB), O_RD = ws_offset(W_RD), O_V1 = ws_offset(W_V1),
-              O_V2 = ws_offset(W_V2), O_OBS = ws_offset(W_OBS), O_GRES = ws_offset(W_GRES);
+              O_V2 = ws_offset(W_V2), O_OBS = ws_offset(W_OBS), O_AUX = ws_offset(W_AUX), O_GRES = ws_offset(W_GRES);
 constexpr int BWD_DEPTH = 4, BWD_SLOT = WS_BWD + 2;                 // backward ring: 4 slots of the [0, WS_BWD) block
 constexpr int FWD_DEPTH = 3, FWD_SLOT = 80 + (WS_FWD1 - WS_FWD0);   // forward ring: AB | GRES KM PV PM, compacted
 constexpr int F_AB = 0, F_GRES = 80, F_KM = F_GRES + 8, F_PV = F_KM + 24, F_PM = F_PV + 10;
 static_assert(BWD_DEPTH * BWD_SLOT <= RING_DOUBLES && FWD_DEPTH * FWD_SLOT <= RING_DOUBLES, "ring too small");
 static_assert(BWD_SLOT % 2 == 0 && FWD_SLOT % 2 == 0, "slot alignment");
 
-__device__ __forceinline__ void stage_fetch_bwd(const Ws& ws, WarpSm& sm, int b, int k, int lane) {
+// A solve step is run by a GROUP of nt threads per instance: one warp (nt = 32, four instances per block) while the
+// batch is large, a whole block (nt = 128 / 384, named barrier) once few instances are left and latency is what counts.
+// Every entry of every matrix is computed by the same arithmetic in both cases, so results do not depend on nt.
+__device__ __forceinline__ void gsync(int nt) {
+    if (nt == 32) __syncwarp();
+    else asm volatile("bar.sync 1, %0;" ::"r"(nt) : "memory");
+}
+
+__device__ __forceinline__ void stage_fetch_bwd(const Ws& ws, WarpSm& sm, int b, int k, int rank, int nt) {
     if (k >= 0) {
         const double* rec = ws.rec(b, k);
         double* dst = sm.ring + (k % BWD_DEPTH) * BWD_SLOT;
-        for (int c = lane; c < WS_BWD / 2; c += 32) cp_async16(dst + 2 * c, rec + 2 * c);
+        for (int c = rank; c < WS_BWD / 2; c += nt) cp_async16(dst + 2 * c, rec + 2 * c);
     }
     cp_async_commit();
 }
-__device__ __forceinline__ void stage_fetch_fwd(const Ws& ws, WarpSm& sm, int b, int k, int H, int lane) {
+__device__ __forceinline__ void stage_fetch_fwd(const Ws& ws, WarpSm& sm, int b, int k, int H, int rank, int nt) {
     if (k < H) {
         const double* rec = ws.rec(b, k);
         double* dst = sm.ring + (k % FWD_DEPTH) * FWD_SLOT;
-        for (int c = lane; c < 40; c += 32) cp_async16(dst + F_AB + 2 * c, rec + O_AB + 2 * c);
-        for (int c = lane; c < (WS_FWD1 - WS_FWD0) / 2; c += 32) cp_async16(dst + F_GRES + 2 * c, rec + WS_FWD0 + 2 * c);
+        for (int c = rank; c < 40; c += nt) cp_async16(dst + F_AB + 2 * c, rec + O_AB + 2 * c);
+        for (int c = rank; c < (WS_FWD1 - WS_FWD0) / 2; c += nt) cp_async16(dst + F_GRES + 2 * c, rec + WS_FWD0 + 2 * c);
     }
     cp_async_commit();
 }
 
-// builds M = [A~ B~] (rows: lifted next state, cols: [x | p | u] of stage k) in shared memory from the staged
-// dynamics Jacobian `ab` ([i][a] stride 8).  M must have been zeroed (and the warp synchronised) before.
-__device__ __forceinline__ void scatter_transition(WarpSm& sm, const double* ab, int lane, const Dims& d, const Dims& dn) {
-    if (d.st) {
-        for (int e = lane; e < dn.nx * 8; e += 32) {
-            const int i = e >> 3, a = e & 7;
-            sm.M[i * 12 + gpos(d, c_act_st[a])] = ab[e];
-        }
-    } else {
-        for (int e = lane; e < dn.nx * 5; e += 32) {
-            const int i = (e * 13108) >> 16, a = e - i * 5;   // e / 5, e % 5 for e < 64
-            sm.M[i * 12 + gpos(d, c_act_pm[a])] = ab[i * 8 + a];
-        }
+// ---- reduced stage state of the Riccati sweeps.  The arclength s and the time t are cyclic coordinates of the
+// linearised problem: s_{k+1} = s_k + ds_k has no control behind it, so its direction is the running sum of the
+// equality residuals and only shifts the linear term of ey (obstacle cross term); t appears in no Hessian block, so its
+// multiplier direction is a running sum of dual residuals that enters the other rows through d t_{k+1} / d y_k.  Both
+// are handled by prefix sums over the stages (lanes over stages) and the matrix recursion runs on
+//   SingleTrack  (Ux Uy r delta ey epsi | lifted u_{k-1})   6 + np        PointMass  (V ey epsi | lifted)   3 + np
+struct RDims { int nxr, np, n, nuo; bool st; };
+__device__ __forceinline__ RDims rdims(int N, int k) {
+    RDims d;
+    d.st = k < N;
+    d.nxr = d.st ? 6 : 3;
+    d.np = k == 0 ? 0 : (d.st ? 1 : 2);
+    d.n = d.nxr + d.np;
+    d.nuo = d.st ? 8 : 5;   // index of the first control inside the stage variable vector y
+    return d;
+}
+// position of ACTIVE variable a (index into c_act_st / c_act_pm) in the Riccati ordering [x^ | p | u]; the first nxr
+// active variables are the reduced state in order, the last two the controls
+__device__ __forceinline__ int apos(const RDims& d, int a) { return a < d.nxr ? a : d.n + (a - d.nxr); }
+// index inside y / inside a full state vector of reduced component i
+__device__ __forceinline__ int yidx(const RDims& d, int i) { return d.st ? c_act_st[i] : c_act_pm[i]; }
+
+// builds M = [A~ B~] (rows: reduced + lifted next state, cols: [x^ | p | u] of stage k) in shared memory from the staged
+// dynamics Jacobian `ab` ([full next-state row][active variable], stride 8).  M must have been zeroed before.
+__device__ __forceinline__ void scatter_transition(WarpSm& sm, const double* ab, int rank, int nt, const RDims& d, const RDims& dn) {
+    const int nact = d.nxr + 2;
+    for (int e = rank; e < dn.nxr * nact; e += nt) {
+        const int i = e / nact, a = e - i * nact;
+        sm.M[i * 12 + apos(d, a)] = ab[yidx(dn, i) * 8 + a];
     }
-    if (lane == 0) {   // s and t pass through with unit derivative
-        sm.M[(dn.st ? IS : QS) * 12 + (d.st ? IS : QS)] = 1.0;
-        sm.M[(dn.st ? IT : QT) * 12 + (d.st ? IT : QT)] = 1.0;
-        sm.M[dn.nx * 12 + d.n] = 1.0;                              // p0 <- Fx_k
-        if (dn.np > 1 && !d.st) sm.M[(dn.nx + 1) * 12 + d.n + 1] = 1.0;   // p1 <- Fy_k
+    if (rank == 31) {
+        sm.M[dn.nxr * 12 + d.n] = 1.0;                                      // p0 <- Fx_k
+        if (dn.np > 1 && !d.st) sm.M[(dn.nxr + 1) * 12 + d.n + 1] = 1.0;    // p1 <- Fy_k
     }
-    if (dn.np > 1 && d.st && lane >= 8 && lane < 16)               // p1 <- T(y_{N-1}) = Fy_f + Fy_r
-        sm.M[(dn.nx + 1) * 12 + gpos(d, c_act_st[lane - 8])] = ab[5 * 8 + lane - 8];
+    if (dn.np > 1 && d.st && rank >= 16 && rank < 24)                       // p1 <- T(y_{N-1}) = Fy_f + Fy_r
+        sm.M[(dn.nxr + 1) * 12 + apos(d, rank - 16)] = ab[5 * 8 + rank - 16];
 }
 
 // ---- stage products of the backward sweep: PMm = P M, tv = P r + p, G += M^T PMm, g += M^T tv
@@ -779,90 +805,160 @@ __device__ __forceinline__ void stage_products(WarpSm& sm, int lane) {
     __syncwarp();
 }
 
+// the same products with one entry per thread (block-wide groups).  `blocked` = the warp path would use the register-
+// blocked template for this shape: there only the upper block triangle of G is computed and mirrored, which this
+// reproduces entry for entry (2x2 blocks: (i,j) with i/2 > j/2 takes the value computed for (j,i)).
+__device__ __forceinline__ void stage_products_wide(WarpSm& sm, int rank, int nt, int dnn, int nn, bool blocked) {
+    for (int e = rank; e < dnn * nn; e += nt) {                 // PMm = P M
+        const int i = e / nn, j = e - i * nn;
+        double acc = 0.0;
+        for (int l = 0; l < dnn; ++l) acc += sm.P[i * 10 + l] * sm.M[l * 12 + j];
+        sm.PMm[i * 12 + j] = acc;
+    }
+    if (rank >= nt - 16 && rank - (nt - 16) < dnn) {            // tv = P r + p
+        const int i = rank - (nt - 16);
+        double a = sm.p[i];
+        for (int l = 0; l < dnn; ++l) a += sm.P[i * 10 + l] * sm.r[l];
+        sm.tv[i] = a;
+    }
+    gsync(nt);
+    for (int e = rank; e < nn * nn; e += nt) {                  // G += M^T (P M)
+        const int i = e / nn, j = e - i * nn;
+        const bool mirror = blocked && (i >> 1) > (j >> 1);
+        const int ii = mirror ? j : i, jj = mirror ? i : j;
+        double acc = 0.0;
+        for (int l = 0; l < dnn; ++l) acc += sm.M[l * 12 + ii] * sm.PMm[l * 12 + jj];
+        sm.G[i * 12 + j] += acc;
+    }
+    if (rank >= nt - 16 && rank - (nt - 16) < nn) {             // g += M^T tv
+        const int c = rank - (nt - 16);
+        double a = 0.0;
+        for (int l = 0; l < dnn; ++l) a += sm.M[l * 12 + c] * sm.tv[l];
+        sm.g[c] += a;
+    }
+    gsync(nt);
+}
+
 // Backward Riccati sweep + forward substitution of the condensed KKT system
 //   [Hc + delta I  Jg^T] [dw  ]   [-(rd - mu v1 + v2)]
 //   [Jg            0   ] [dlam] = [-g                ]
 // Returns false when some reduced Hessian block is not positive definite (wrong inertia for this delta).
 // The per-stage blocks are streamed through a shared-memory ring with cp.async, several stages ahead of the math.
-__device__ __noinline__ bool riccati(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int lane, double mu, double delta, bool soc) {
+// warp prefix / suffix sums (inclusive) used by the s / t passes
+__device__ __forceinline__ double warp_scan_up(double v, int lane) {
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const double t = __shfl_up_sync(FULL, v, o); if (lane >= o) v += t; }
+    return v;
+}
+__device__ __forceinline__ double warp_scan_down(double v, int lane) {
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const double t = __shfl_down_sync(FULL, v, o); if (lane + o < 32) v += t; }
+    return v;
+}
+
+__device__ __noinline__ bool riccati(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int rank, int nt, double mu, double delta, bool soc) {
     const int H = pr.H, N = pr.N;
     // second-order correction: same matrix, residuals replaced by the accumulated c_soc (IPOPT 2.4 / Alg. A-5.7)
     const int a_gres = soc ? W_GS : W_GRES, a_dy = soc ? W_DY2 : W_DY, a_dlam = soc ? W_DLAM2 : W_DLAM;
     const double sf = ws.scal(b)[S_SF];
     bool ok = true;
-    __syncwarp();
-    for (int j = 1; j < BWD_DEPTH; ++j) stage_fetch_bwd(ws, sm, b, H - j, lane);
+    // ---- pre-pass (first warp, lanes over stages): direction of s = running sum of its equality residuals;
+    // cost-to-go gradient of t = running sum (from the end) of its dual residuals
+    if (rank < 32) {
+        double carry = 0.0;
+        for (int base = 0; base < H; base += 32) {
+            const int k = base + rank;
+            double v = k < H ? -ws.at(b, a_gres, k)[k < N ? IS : QS] : 0.0;
+            v = warp_scan_up(v, rank) + carry;
+            if (k < H) { ws.at(b, a_dy, k)[k < N ? IS : QS] = v; ws.at(b, W_AUX, k)[0] = v; }
+            carry = __shfl_sync(FULL, v, 31);
+        }
+        carry = 0.0;
+        for (int base = ((H - 1) / 32) * 32; base >= 0; base -= 32) {
+            const int k = base + rank;
+            double v = k < H ? ws.at(b, W_RD, k)[k < N ? IT : QT] : 0.0;
+            v = warp_scan_down(v, rank) + carry;
+            if (k < H) {
+                ws.at(b, a_dlam, k)[k < N ? IT : QT] = -v;
+                if (k >= 1) ws.at(b, W_AUX, k - 1)[1] = v;
+                if (k == H - 1) ws.at(b, W_AUX, k)[1] = 0.0;
+            }
+            carry = __shfl_sync(FULL, v, 0);
+        }
+    }
+    gsync(nt);
+    for (int j = 1; j < BWD_DEPTH; ++j) stage_fetch_bwd(ws, sm, b, H - j, rank, nt);
     for (int k = H - 1; k >= 0; --k) {
-        stage_fetch_bwd(ws, sm, b, k - (BWD_DEPTH - 1), lane);
-        const Dims d = stage_dims(N, k);
-        const int n = d.n, nn = n + 2;
+        stage_fetch_bwd(ws, sm, b, k - (BWD_DEPTH - 1), rank, nt);
+        const RDims d = rdims(N, k);
+        const int n = d.n, nn = n + 2, nact = d.nxr + 2;
         const int rcp_nn = 65536 / nn + 1, rcp_n = 65536 / n + 1;
-        for (int e = lane; e < 144; e += 32) sm.G[e] = 0.0;
-        for (int e = lane; e < 120; e += 32) sm.M[e] = 0.0;
+        for (int e = rank; e < 144; e += nt) sm.G[e] = 0.0;
+        for (int e = rank; e < 120; e += nt) sm.M[e] = 0.0;
         cp_async_wait<BWD_DEPTH - 1>();
-        __syncwarp();
+        gsync(nt);
         const double* sb = sm.ring + (k % BWD_DEPTH) * BWD_SLOT;
         {   // stage Hessian block over the active variables
             const int npair = d.st ? 36 : 15;
-            for (int q = lane; q < npair; q += 32) {
+            for (int q = rank; q < npair; q += nt) {
                 int ia = (int)((sqrtf(8.0f * q + 1.0f) - 1.0f) * 0.5f);
                 if ((ia + 1) * (ia + 2) / 2 <= q) ++ia;
                 if (ia * (ia + 1) / 2 > q) --ia;
                 const int ib = q - ia * (ia + 1) / 2;
-                const int pa = gpos(d, d.st ? c_act_st[ia] : c_act_pm[ia]), pb = gpos(d, d.st ? c_act_st[ib] : c_act_pm[ib]);
+                const int pa = apos(d, ia), pb = apos(d, ib);
                 const double v = sb[O_HC + q];
                 sm.G[pa * 12 + pb] = v;
                 sm.G[pb * 12 + pa] = v;
             }
-            if (lane < d.nx + 2) {
-                double f = sb[O_RD + lane] - mu * sb[O_V1 + lane] + sb[O_V2 + lane];
+            // linear term of active variable a on lane a of the LAST warp of the group
+            const int a = rank - (nt - 32);
+            if (a >= 0 && a < nact) {
+                const int yi = yidx(d, a);   // (a >= nxr: the controls, which c_act_* lists last)
+                double f = sb[O_RD + yi] - mu * sb[O_V1 + yi] + sb[O_V2 + yi];
                 if (soc) {   // + Jc^T sigma (c_soc - (c - s))
-                    const int a = d.st ? (lane < 4 ? lane : lane == 5 ? 4 : lane == 6 ? 5 : lane >= 8 ? lane - 2 : -1)
-                                       : (lane == 0 ? 0 : lane == 2 ? 1 : lane == 3 ? 2 : lane >= 5 ? lane - 2 : -1);
-                    if (a >= 0) {
-                        const double *jc = ws.at(b, W_JC, k), *cs = ws.at(b, W_CS, k), *cr = ws.at(b, W_CRES, k);
-                        const double *s = ws.at(b, W_S, k), *z = ws.at(b, W_Z, k);
-                        for (int j = 0; j < (d.st ? NI_ST : NI_PM); ++j)
-                            f += jc[j * 8 + a] * (z[j] / s[j]) * (cs[j] - (cr[j] - s[j]));
-                    }
+                    const double *jc = ws.at(b, W_JC, k), *cs = ws.at(b, W_CS, k), *cr = ws.at(b, W_CRES, k);
+                    const double *sl = ws.at(b, W_S, k), *z = ws.at(b, W_Z, k);
+                    for (int j = 0; j < (d.st ? NI_ST : NI_PM); ++j)
+                        f += jc[j * 8 + a] * (z[j] / sl[j]) * (cs[j] - (cr[j] - sl[j]));
                 }
-                sm.g[gpos(d, lane)] = f;
+                if (yi == (d.st ? IEY : QEY)) f += sf * sb[O_OBS + 4] * sb[O_AUX];          // obstacle cross term (s, ey) x ds
+                if (k < H - 1) f += sb[O_AB + (k + 1 < N ? IT : QT) * 8 + a] * sb[O_AUX + 1];   // d t_{k+1} / d a x cost-to-go of t
+                sm.g[apos(d, a)] = f;
             }
-            if (lane >= d.nx && lane < n) sm.g[lane] = 0.0;   // lifted variables carry no linear term
-            if (k < H - 1) scatter_transition(sm, sb + O_AB, lane, d, stage_dims(N, k + 1));
+            if (a >= d.nxr + 2 && a < d.nxr + 2 + d.np) sm.g[a - 2] = 0.0;   // lifted variables carry no linear term
+            if (k < H - 1) scatter_transition(sm, sb + O_AB, rank, nt, d, rdims(N, k + 1));
         }
-        __syncwarp();
-        {   // closed-form Hessian parts: obstacle term (lane 0), control-continuity terms (lanes 1, 2), delta_w
+        gsync(nt);
+        {   // closed-form Hessian parts: obstacle term (rank 0), control-continuity terms (ranks 1, 2), delta_w
             const double* ob = sb + O_OBS;
-            if (lane == 0) {
-                const int si = d.st ? IS : QS, eyi = d.st ? IEY : QEY;
-                sm.G[si * 12 + si] += sf * ob[3];
-                sm.G[si * 12 + eyi] += sf * ob[4];
-                sm.G[eyi * 12 + si] += sf * ob[4];
-                sm.G[eyi * 12 + eyi] += sf * ob[5];
-            } else if (lane <= d.np) {
-                const int j = lane - 1;
+            if (rank == 0) {
+                const int eyp = d.st ? 4 : 1;
+                sm.G[eyp * 12 + eyp] += sf * ob[5];
+            } else if (rank <= d.np) {
+                const int j = rank - 1;
                 const double cc = 2.0 * sf * ob[6 + j];
                 sm.G[(n + j) * 12 + n + j] += cc;
-                sm.G[(d.nx + j) * 12 + d.nx + j] += cc;
-                sm.G[(n + j) * 12 + d.nx + j] -= cc;
-                sm.G[(d.nx + j) * 12 + n + j] -= cc;
+                sm.G[(d.nxr + j) * 12 + d.nxr + j] += cc;
+                sm.G[(n + j) * 12 + d.nxr + j] -= cc;
+                sm.G[(d.nxr + j) * 12 + n + j] -= cc;
             }
             if (delta != 0.0) {
-                __syncwarp();
-                if (lane < d.nx) sm.G[lane * 12 + lane] += delta;
-                if (lane >= 30) sm.G[(n + lane - 30) * 12 + n + lane - 30] += delta;
+                gsync(nt);
+                if (rank < d.nxr) sm.G[rank * 12 + rank] += delta;
+                if (rank >= 30 && rank < 32) sm.G[(n + rank - 30) * 12 + n + rank - 30] += delta;
             }
         }
-        __syncwarp();
+        gsync(nt);
         if (k < H - 1) {
-            const Dims dn = stage_dims(N, k + 1);
+            const RDims dn = rdims(N, k + 1);
             // G += M^T P M, g += M^T (P r + p): register-blocked for the stage shapes of the shipped controllers
-            if (dn.n == 9 && nn == 11) stage_products<9, 11>(sm, lane);
-            else if (dn.n == 7 && nn == 9) stage_products<7, 9>(sm, lane);
-            else if (dn.n == 7 && nn == 11) stage_products<7, 11>(sm, lane);
-            else if (dn.n == 9 && nn == 10) stage_products<9, 10>(sm, lane);
-            else stage_products_generic(sm, lane, dn.n, nn, rcp_nn);
+            const bool blocked = (dn.n == 7 && (nn == 9 || nn == 8)) || (dn.n == 5 && (nn == 7 || nn == 9));
+            if (nt != 32) stage_products_wide(sm, rank, nt, dn.n, nn, blocked);
+            else if (dn.n == 7 && nn == 9) stage_products<7, 9>(sm, rank);
+            else if (dn.n == 5 && nn == 7) stage_products<5, 7>(sm, rank);
+            else if (dn.n == 5 && nn == 9) stage_products<5, 9>(sm, rank);
+            else if (dn.n == 7 && nn == 8) stage_products<7, 8>(sm, rank);
+            else stage_products_generic(sm, rank, dn.n, nn, rcp_nn);
         }
         // reduced Hessian of the two controls
         const double ra = sm.G[n * 12 + n], rb = 0.5 * (sm.G[n * 12 + n + 1] + sm.G[(n + 1) * 12 + n]),
@@ -872,24 +968,27 @@ __device__ __noinline__ bool riccati(const Prob& pr, const Ws& ws, WarpSm& sm, i
         const double idet = 1.0 / det;
         const double i00 = rdd * idet, i01 = -rb * idet, i11 = ra * idet;
         double* km = ws.at(b, W_KM, k);
-        if (lane < n) {
-            const double g0 = sm.G[n * 12 + lane], g1 = sm.G[(n + 1) * 12 + lane];
+        if (rank < n) {
+            const double g0 = sm.G[n * 12 + rank], g1 = sm.G[(n + 1) * 12 + rank];
             const double k0 = -(i00 * g0 + i01 * g1), k1 = -(i01 * g0 + i11 * g1);
-            sm.K[lane] = k0; sm.K[12 + lane] = k1;
-            km[lane] = k0; km[10 + lane] = k1;
+            sm.K[rank] = k0; sm.K[12 + rank] = k1;
+            km[rank] = k0; km[10 + rank] = k1;
         }
-        if (lane == 31) {
+        if (rank == 31) {
             const double g0 = sm.g[n], g1 = sm.g[n + 1];
             const double f0 = -(i00 * g0 + i01 * g1), f1 = -(i01 * g0 + i11 * g1);
             sm.K[10] = f0; sm.K[22] = f1;
             km[20] = f0; km[21] = f1;
         }
         // the equality residual of THIS stage's state is the offset of the transition into it (used at stage k-1)
-        if (lane < 12) sm.r[lane] = lane < d.nx ? -(soc ? ws.at(b, a_gres, k)[lane] : sb[O_GRES + lane]) : 0.0;
-        __syncwarp();
+        if (rank >= 12 && rank < 24) {
+            const int q = rank - 12;
+            sm.r[q] = q < d.nxr ? -(soc ? ws.at(b, a_gres, k)[yidx(d, q)] : sb[O_GRES + yidx(d, q)]) : 0.0;
+        }
+        gsync(nt);
         double* pm = ws.at(b, W_PM, k);
         double* pv = ws.at(b, W_PV, k);
-        for (int e = lane; e < n * n; e += 32) {               // P = Gxx + Gxu K   (symmetrised)
+        for (int e = rank; e < n * n; e += nt) {               // P = Gxx + Gxu K   (symmetrised)
             const int i = (e * rcp_n) >> 16, j = e - i * n;
             const double a = sm.G[i * 12 + j] + sm.G[i * 12 + n] * sm.K[j] + sm.G[i * 12 + n + 1] * sm.K[12 + j];
             const double c = sm.G[j * 12 + i] + sm.G[j * 12 + n] * sm.K[i] + sm.G[j * 12 + n + 1] * sm.K[12 + i];
@@ -897,65 +996,136 @@ __device__ __noinline__ bool riccati(const Prob& pr, const Ws& ws, WarpSm& sm, i
             sm.P[i * 10 + j] = v;
             pm[i * 10 + j] = v;
         }
-        if (lane < n) {
-            const double v = sm.g[lane] + sm.G[lane * 12 + n] * sm.K[10] + sm.G[lane * 12 + n + 1] * sm.K[22];
-            sm.p[lane] = v;
-            pv[lane] = v;
+        {
+            const int q = rank - (nt - 16);                    // last half-warp of the group
+            if (q >= 0 && q < n) {
+                const double v = sm.g[q] + sm.G[q * 12 + n] * sm.K[10] + sm.G[q * 12 + n + 1] * sm.K[22];
+                sm.p[q] = v;
+                pv[q] = v;
+            }
         }
-        __syncwarp();
+        gsync(nt);
     }
     cp_async_wait<0>();
-    __syncwarp();
+    gsync(nt);
     if (!ok) return false;
     // ---- forward substitution (stage blocks AB | GRES KM PV PM streamed two stages ahead)
-    for (int j = 0; j < FWD_DEPTH - 1; ++j) stage_fetch_fwd(ws, sm, b, j, H, lane);
-    stage_fetch_fwd(ws, sm, b, FWD_DEPTH - 1, H, lane);
+    for (int j = 0; j < FWD_DEPTH - 1; ++j) stage_fetch_fwd(ws, sm, b, j, H, rank, nt);
+    stage_fetch_fwd(ws, sm, b, FWD_DEPTH - 1, H, rank, nt);
     cp_async_wait<FWD_DEPTH - 1>();
-    __syncwarp();
-    if (lane < 12) sm.x[lane] = lane < 8 ? -(soc ? ws.at(b, a_gres, 0)[lane] : sm.ring[F_GRES + lane]) : 0.0;
-    __syncwarp();
+    gsync(nt);
+    if (rank < 12) {
+        const RDims d0 = rdims(N, 0);
+        sm.x[rank] = rank < d0.nxr ? -(soc ? ws.at(b, a_gres, 0)[yidx(d0, rank)] : sm.ring[F_GRES + yidx(d0, rank)]) : 0.0;
+    }
+    gsync(nt);
     for (int k = 0; k < H; ++k) {
-        const Dims d = stage_dims(N, k);
+        const RDims d = rdims(N, k);
         const int n = d.n;
         const double* fb = sm.ring + (k % FWD_DEPTH) * FWD_SLOT;
-        if (lane < 2) {
+        if (rank < 2) {
             const double* km = fb + F_KM;
-            double a = km[20 + lane];
-            for (int l = 0; l < n; ++l) a += km[lane * 10 + l] * sm.x[l];
-            sm.x[n + lane] = a;
+            double a = km[20 + rank];
+            for (int l = 0; l < n; ++l) a += km[rank * 10 + l] * sm.x[l];
+            sm.x[n + rank] = a;
         }
-        if (k < H - 1) for (int e = lane; e < 120; e += 32) sm.M[e] = 0.0;
-        __syncwarp();
+        if (k < H - 1) for (int e = rank; e < 120; e += nt) sm.M[e] = 0.0;
+        gsync(nt);
         double* dy = ws.at(b, a_dy, k);
-        if (lane < d.nx) {
-            dy[lane] = sm.x[lane];
-            const double* pm = fb + F_PM;
-            double a = fb[F_PV + lane];
-            for (int l = 0; l < n; ++l) a += pm[lane * 10 + l] * sm.x[l];
-            ws.at(b, a_dlam, k)[lane] = -a;
+        {
+            const int q = rank - (nt - 16);                    // multiplier direction on the last half-warp
+            if (q >= 0 && q < d.nxr) {
+                const double* pm = fb + F_PM;
+                double a = fb[F_PV + q];
+                for (int l = 0; l < n; ++l) a += pm[q * 10 + l] * sm.x[l];
+                ws.at(b, a_dlam, k)[yidx(d, q)] = -a;
+            }
         }
-        if (lane < 2) dy[d.nu_off + lane] = sm.x[n + lane];
+        if (rank < d.nxr) dy[yidx(d, rank)] = sm.x[rank];
+        if (rank < 2) dy[d.nuo + rank] = sm.x[n + rank];
         if (k < H - 1) {
-            const Dims dn = stage_dims(N, k + 1);
-            scatter_transition(sm, fb + F_AB, lane, d, dn);
+            const RDims dn = rdims(N, k + 1);
+            scatter_transition(sm, fb + F_AB, rank, nt, d, dn);
             cp_async_wait<FWD_DEPTH - 2>();     // stage k+1's block (its GRES is the offset of this transition)
-            __syncwarp();
+            gsync(nt);
             const double* fn = sm.ring + ((k + 1) % FWD_DEPTH) * FWD_SLOT;
             double a = 0.0;
-            if (lane < dn.n) {
-                a = lane < dn.nx ? -(soc ? ws.at(b, a_gres, k + 1)[lane] : fn[F_GRES + lane]) : 0.0;
-                for (int l = 0; l < n + 2; ++l) a += sm.M[lane * 12 + l] * sm.x[l];
+            if (rank < dn.n) {
+                a = rank < dn.nxr ? -(soc ? ws.at(b, a_gres, k + 1)[yidx(dn, rank)] : fn[F_GRES + yidx(dn, rank)]) : 0.0;
+                for (int l = 0; l < n + 2; ++l) a += sm.M[rank * 12 + l] * sm.x[l];
             }
-            __syncwarp();
-            if (lane < dn.n) sm.x[lane] = a;
+            gsync(nt);
+            if (rank < dn.n) sm.x[rank] = a;
             // slot of stage k is free now: stream stage k + FWD_DEPTH into it
-            stage_fetch_fwd(ws, sm, b, k + FWD_DEPTH, H, lane);
-            __syncwarp();
+            stage_fetch_fwd(ws, sm, b, k + FWD_DEPTH, H, rank, nt);
+            gsync(nt);
         }
     }
     cp_async_wait<0>();
-    __syncwarp();
+    gsync(nt);
+    // ---- post-pass (first warp, lanes over stages): direction of t = running sum of its linearised increments;
+    // multiplier direction of s = running sum (from the end) of its stationarity row
+    if (rank < 32) {
+        double carry = 0.0;
+        for (int base = 0; base < H; base += 32) {
+            const int k = base + rank;
+            double v = 0.0;
+            if (k < H) {
+                v = -ws.at(b, a_gres, k)[k < N ? IT : QT];
+                if (k >= 1) {
+                    const RDims dp = rdims(N, k - 1);
+                    const double* ab = ws.at(b, W_AB, k - 1) + (k < N ? IT : QT) * 8;
+                    const double* dyp = ws.at(b, a_dy, k - 1);
+                    for (int a = 0; a < dp.nxr + 2; ++a) v += ab[a] * dyp[yidx(dp, a)];
+                }
+            }
+            v = warp_scan_up(v, rank) + carry;
+            if (k < H) ws.at(b, a_dy, k)[k < N ? IT : QT] = v;
+            carry = __shfl_sync(FULL, v, 31);
+        }
+        carry = 0.0;
+        for (int base = ((H - 1) / 32) * 32; base >= 0; base -= 32) {
+            const int k = base + rank;
+            double v = 0.0;
+            if (k < H) {
+                const double* ob = ws.at(b, W_OBS, k);
+                const double* dyk = ws.at(b, a_dy, k);
+                v = ws.at(b, W_RD, k)[k < N ? IS : QS] + sf * (ob[3] * dyk[k < N ? IS : QS] + ob[4] * dyk[k < N ? IEY : QEY]);
+            }
+            v = warp_scan_down(v, rank) + carry;
+            if (k < H) ws.at(b, a_dlam, k)[k < N ? IS : QS] = -v;
+            carry = __shfl_sync(FULL, v, 0);
+        }
+    }
+    gsync(nt);
     return true;
+}
+
+// ---- helper threads of a block-wide group: warp 0 runs the (scalar) interior-point logic of its instance and calls
+// the others in for the factorisations.  Commands go through shared memory, hand-over by the named barrier.
+enum GroupOp { OP_EXIT = 0, OP_RICCATI = 1 };
+struct GroupCmd { int op, soc; double mu, delta; };
+struct Group { int rank, nt; GroupCmd* cmd; };   // cmd == nullptr for a warp group
+
+__device__ __forceinline__ bool riccati_call(const Prob& pr, const Ws& ws, WarpSm& sm, int b, const Group& g, double mu, double delta, bool soc) {
+    if (g.nt != 32) {
+        if (g.rank == 0) { g.cmd->op = OP_RICCATI; g.cmd->soc = soc; g.cmd->mu = mu; g.cmd->delta = delta; }
+        gsync(g.nt);   // releases the helpers (group_helpers)
+    }
+    return riccati(pr, ws, sm, b, g.rank, g.nt, mu, delta, soc);
+}
+__device__ __forceinline__ void group_helpers(const Prob& pr, const Ws& ws, WarpSm& sm, int b, const Group& g) {
+    for (;;) {
+        gsync(g.nt);
+        const GroupCmd c = *g.cmd;
+        if (c.op == OP_EXIT) return;
+        riccati(pr, ws, sm, b, g.rank, g.nt, c.mu, c.delta, c.soc != 0);
+    }
+}
+__device__ __forceinline__ void group_release(const Group& g) {   // called by warp 0 when its instance's step is finished
+    if (g.nt == 32) return;
+    if (g.rank == 0) g.cmd->op = OP_EXIT;
+    gsync(g.nt);
 }
 
 // slack / multiplier directions of a computed primal direction, fraction-to-the-boundary step sizes and the
@@ -1100,235 +1270,19 @@ __device__ __noinline__ bool rollout_sane(const Prob& pr, const Ws& ws, int b) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// k_step: one interior-point iteration of every unfinished instance (one warp each)
-__device__ void step_instance(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int lane) {
-    double* sc = ws.scal(b);
-    const int mode = (int)sc[S_MODE];
-    if (mode == MODE_DONE) return;
-    const int H = pr.H, N = pr.N, M = pr.M;
-    const Cfg& c = pr.c;
-    const Measures m = finish_gradients(pr, ws, b, lane);
-    const bool finite = isfinite(m.f) && isfinite(m.theta) && isfinite(m.rdmax) && isfinite(m.prim);
-    double mu = sc[S_MU];
-    const double sf = sc[S_SF];
-    if (mode == MODE_INIT || mode == MODE_REINIT) {
-        if (!finite) {   // invalid starting point (NaN / inside an obstacle pole): restoration substitute, else give up
-            const int restarts = (int)sc[S_RESTARTS];
-            if (restarts >= 2) { finalize(pr, ws, b, lane, VC_EVAL_ERROR, m.f, INFINITY); return; }
-            __syncwarp();
-            // (an invalid FIRST point has no gradient to scale by: the repaired point then sets the objective scaling)
-            if (lane == 0) { repair_rollout(pr, ws, b); sc[S_RESTARTS] = restarts + 1; sc[S_MODE] = mode; }
-            return;
-        }
-        if (mode == MODE_INIT && c.obj_scaling && m.gfmax > IpmConst::max_gradient && lane == 0)
-            sc[S_SF] = IpmConst::max_gradient / m.gfmax;   // gradient-based objective scaling at the initial point
-        init_slacks(pr, ws, b, lane, mu);
-        if (lane == 0) { sc[S_MODE] = MODE_STEP; sc[S_NFILT] = 0; sc[S_THETA0] = -1.0; sc[S_ACC] = 0; }
-        return;
-    }
-    // ---- convergence test (IPOPT overall error E_0) and barrier update
-    const int me = 8 + 8 * (N - 1) + (M > 0 ? 5 * M : 0), mi = NI_ST * N + NI_PM * M;
-    const double sd = fmax(IpmConst::s_max, (m.sumlam + m.sumz) / (me + mi)) / IpmConst::s_max;
-    const double scs = fmax(IpmConst::s_max, m.sumz / mi) / IpmConst::s_max;
-    const double e_dp = fmax(m.rdmax / sd, m.prim);
-    const double err0 = fmax(e_dp, compl_error(pr, ws, b, lane, 0.0) / scs);
-    const double obj = m.f;
-    int iters = (int)sc[S_ITERS];
-    if (!finite) { finalize(pr, ws, b, lane, VC_EVAL_ERROR, obj, INFINITY); return; }
-    if (err0 <= c.tol) { finalize(pr, ws, b, lane, VC_SOLVED, obj, err0); return; }
-    int acc = (err0 <= c.acceptable_tol) ? (int)sc[S_ACC] + 1 : 0;
-    if (acc >= c.acceptable_iter) { finalize(pr, ws, b, lane, VC_ACCEPTABLE, obj, err0); return; }
-    if (iters >= c.max_iter) { finalize(pr, ws, b, lane, VC_MAX_ITER, obj, err0); return; }
-    int nfilt = (int)sc[S_NFILT];
-    const double mu_floor = c.tol / 11.0;
-    while (mu > mu_floor * (1 + 1e-12) &&
-           fmax(e_dp, compl_error(pr, ws, b, lane, mu) / scs) <= IpmConst::kappa_eps * mu) {
-        mu = fmax(mu_floor, fmin(IpmConst::kappa_mu * mu, pow(mu, IpmConst::theta_mu)));
-        nfilt = 0;
-    }
-    // stall escape (stands in for IPOPT's watchdog): several consecutive heavily shortened steps mean the Newton
-    // model of this barrier problem is poor where the iterate sits; the barrier problem need not be solved
-    // accurately for path following, so move on to the next rung
-    int n_short = (int)sc[S_SHORT];
-    if (n_short >= pr.stall_iters && mu > mu_floor * (1 + 1e-12)) {
-        mu = fmax(mu_floor, fmin(IpmConst::kappa_mu * mu, pow(mu, IpmConst::theta_mu)));
-        nfilt = 0; n_short = 0;
-    }
-    // feasibility restoration substitute: a run of heavily shortened steps at an infeasible iterate means the
-    // linearisation is poor there (IPOPT would end up in its restoration phase); project the iterate onto the
-    // dynamics manifold by rolling the models out from x0 under the CURRENT controls and restart the barrier
-    // problem from that point (same mu, cleared filter)
-    if (pr.restore_iters > 0 && n_short >= pr.restore_iters && (int)sc[S_NREST] < 3 && m.theta > 1e-6) {
-        __syncwarp();
-        if (lane == 0) {
-            repair_rollout(pr, ws, b, false);
-            if (pr.restore_check && !rollout_sane(pr, ws, b)) repair_rollout(pr, ws, b, true);   // neutral controls instead
-            sc[S_NREST] += 1.0; sc[S_MODE] = MODE_REINIT; sc[S_SHORT] = 0; sc[S_ITERS] = iters + 1; sc[S_MU] = mu;
-        }
-        for (int k = lane; k < H; k += 32) {
-            double *lam = ws.at(b, W_LAM, k), *s = ws.at(b, W_S, k), *z = ws.at(b, W_Z, k);
-            for (int i = 0; i < 8; ++i) lam[i] = 0.0;
-            for (int j = 0; j < 10; ++j) { s[j] = 1.0; z[j] = 0.0; }
-        }
-        return;
-    }
-    // all restorations used and the steps are still being cut at an infeasible iterate: give the instance up (IPOPT ends
-    // such runs with "restoration failed"); it would otherwise crawl to max_iter and hold the whole batch's tail
-    if (pr.restore_iters > 0 && (int)sc[S_NREST] >= 3 && n_short >= pr.giveup_iters && m.theta > 1e-6 &&
-        !(mu > mu_floor * (1 + 1e-12))) {
-        finalize(pr, ws, b, lane, VC_LINESEARCH_FAIL, obj, err0);
-        return;
-    }
-    const double tau = fmax(IpmConst::tau_min, 1.0 - mu);
-    const double theta = m.theta, phi = sf * m.f - mu * m.lns;
-    double theta0 = sc[S_THETA0];
-    if (theta0 < 0.0) theta0 = theta;
-    const double theta_min = 1e-4 * fmax(1.0, theta0), theta_max = 1e4 * fmax(1.0, theta0);
-    const double delta_last = sc[S_DELTA_LAST];
-    const bool first_ever = delta_last == 0.0;
-    double trial = 0.0, alpha = 0.0, a_d = 1.0, dbg_ap = 0.0, dbg_dphi = 0.0, dbg_tht0 = 0.0, dbg_pht0 = 0.0;
-    int dbg_nan = 0;
-    double dbg_tht2 = 0.0, dbg_ap2 = 0.0;
-    bool accepted = false, failed = false;
-    int n_damp = 0;
-    double* filt_t = sc + S_FILT;
-    double* filt_p = sc + S_FILP;
-    bool use_soc = false;
-    // acceptance of a trial point by the filter (IPOPT Alg. A, steps A-5.3/5.4); all lanes hold the same values
-    auto acceptable = [&](double a_test, double tht, double pht, double dphi, bool& augment) -> bool {
-        augment = false;
-        if (tht > theta_max) return false;
-        for (int i = 0; i < nfilt; ++i)
-            if (tht >= filt_t[i] && pht >= filt_p[i]) return false;
-        const bool switching = theta <= theta_min && dphi < 0.0 &&
-                               a_test * pow(-dphi, IpmConst::s_phi) > IpmConst::delta * pow(theta, IpmConst::s_theta);
-        if (switching) {
-            if (pht <= phi + IpmConst::eta_phi * a_test * dphi) return true;
-        } else if (tht <= (1 - IpmConst::gamma_theta) * theta || pht <= phi - IpmConst::gamma_phi * theta) {
-            augment = true;
-            return true;
-        }
-        // steps at the rounding floor: both measures unchanged
-        return fabs(pht - phi) <= 1e-13 * fmax(1.0, fabs(phi)) && tht <= theta + 1e-13;
-    };
-    while (!accepted && !failed) {
-        // ---- inertia-correcting factorisation (IPOPT delta_w ladder)
-        while (!riccati(pr, ws, sm, b, lane, mu, trial, false)) {
-            if (trial == 0.0) trial = first_ever ? 1e-4 : fmax(1e-20, delta_last / 3.0);
-            else trial *= first_ever ? 100.0 : 8.0;
-            if (trial > 1e40) { failed = true; break; }
-        }
-        if (failed) break;
-        double a_p, dphi;
-        slack_directions(pr, ws, b, lane, mu, tau, false, a_p, a_d, dphi);
-        dbg_ap = a_p; dbg_dphi = dphi;
-        // ---- backtracking filter line search, lanes over stages
-        alpha = a_p;
-        for (int bt = 0; bt < 12 && !accepted; ++bt, alpha *= 0.5) {
-            double ft, tht, lnt;
-            const bool okv = trial_point(pr, ws, b, lane, alpha, false, bt == 0, ft, tht, lnt);
-            if (!okv) ++dbg_nan;
-            if (bt == 0) { dbg_tht0 = tht; dbg_pht0 = sf * ft - mu * lnt; }
-            bool augment = false;
-            if (okv && acceptable(alpha, tht, sf * ft - mu * lnt, dphi, augment)) accepted = true;
-            // ---- second-order correction (IPOPT Alg. A-5.5 .. A-5.9): first trial step rejected and infeasibility
-            // not reduced -> re-solve with c_soc = alpha c(x) + c(x + alpha d), at most 4 times
-            if (!accepted && bt == 0 && okv && tht >= theta && pr.max_soc > 0) {
-                soc_residual(pr, ws, b, lane, alpha, false, true);
-                double theta_soc_old = theta;
-                for (int ps = 0; ps < pr.max_soc; ++ps) {
-                    if (!riccati(pr, ws, sm, b, lane, mu, trial, true)) break;
-                    double a_p2, a_d2, dphi2, ft2, tht2, lnt2;
-                    slack_directions(pr, ws, b, lane, mu, tau, true, a_p2, a_d2, dphi2);
-                    const bool ok2 = trial_point(pr, ws, b, lane, a_p2, true, true, ft2, tht2, lnt2);
-                    if (ps == 0) { dbg_tht2 = ok2 ? tht2 : -1.0; dbg_ap2 = a_p2; }
-                    if (ok2 && acceptable(alpha, tht2, sf * ft2 - mu * lnt2, dphi, augment)) {
-                        accepted = true; use_soc = true; alpha = a_p2; a_d = a_d2;
-                        break;
-                    }
-                    if (!ok2 || tht2 > 0.99 * theta_soc_old) break;
-                    theta_soc_old = tht2;
-                    soc_residual(pr, ws, b, lane, a_p2, true, false);
-                }
-            }
-            if (accepted) {
-                if (augment && nfilt < FILT_MAX) {
-                    if (lane == 0) { filt_t[nfilt] = (1 - IpmConst::gamma_theta) * theta; filt_p[nfilt] = phi - IpmConst::gamma_phi * theta; }
-                    ++nfilt;
-                }
-                break;
-            }
-        }
-        __syncwarp();
-        if (accepted) break;
-        // no acceptable step along this direction: damp it (larger delta_w) and retry; IPOPT would restore here
-        trial = fmax(trial, 1e-4) * 100.0;
-        if (trial > 1e12 || ++n_damp > pr.max_damp) failed = true;
-    }
-    if (failed) {
-        const int restarts = (int)sc[S_RESTARTS];
-        if (restarts >= 2) { finalize(pr, ws, b, lane, VC_LINESEARCH_FAIL, obj, err0); return; }
-        __syncwarp();
-        if (lane == 0) {
-            repair_rollout(pr, ws, b);
-            sc[S_RESTARTS] = restarts + 1; sc[S_MODE] = MODE_REINIT; sc[S_MU] = c.mu_init; sc[S_DELTA_LAST] = 0.0;
-            sc[S_ITERS] = iters + 1;
-        }
-        for (int k = lane; k < H; k += 32) {   // neutral multipliers / slacks for the re-evaluation
-            double *lam = ws.at(b, W_LAM, k), *s = ws.at(b, W_S, k), *z = ws.at(b, W_Z, k);
-            for (int i = 0; i < 8; ++i) lam[i] = 0.0;
-            for (int j = 0; j < 10; ++j) { s[j] = 1.0; z[j] = 0.0; }
-        }
-        return;
-    }
-    // ---- accept: primal-dual update with the z safeguard (IPOPT kappa_sigma).  The iterate [y | lam | s] and the
-    // direction [dy | dlam | dsl] are 28 contiguous doubles of each stage record: lanes run over (stage, element) so
-    // that the loads coalesce and are independent (a lane-per-stage loop serialises 38 global round trips per lane)
-    {
-        const int odir = use_soc ? O_DIR2 : O_DIR;
-        double* rec0 = ws.rec(b, 0);
-#pragma unroll 4
-        for (int e = lane; e < H * 28; e += 32) {
-            const int k = e / 28, i = e - k * 28;
-            const bool st = k < N;
-            const bool used = i < 10 ? i < (st ? 10 : 7) : (i < 18 ? i - 10 < (st ? 8 : 5) : i - 18 < (st ? NI_ST : NI_PM));
-            if (used) {
-                double* r = rec0 + (size_t)k * WS_PER_STAGE;
-                r[O_IT + i] += alpha * r[odir + i];
-            }
-        }
-        __syncwarp();
-#pragma unroll 4
-        for (int e = lane; e < H * 10; e += 32) {
-            const int k = e / 10, j = e - k * 10;
-            if (j < (k < N ? NI_ST : NI_PM)) {
-                double* r = rec0 + (size_t)k * WS_PER_STAGE;
-                const double sj = r[O_IT + 18 + j];
-                double zj = r[O_IT + 28 + j] + a_d * r[odir + 28 + j];
-                zj = fmin(fmax(zj, mu / (IpmConst::kappa_sigma * sj)), IpmConst::kappa_sigma * mu / sj);
-                r[O_IT + 28 + j] = zj;
-            }
-        }
-    }
-    if (lane == 0) {
-        sc[S_SHORT] = (alpha < 0.05 * dbg_ap && !use_soc) ? n_short + 1 : 0;
-        sc[S_MU] = mu; sc[S_NFILT] = nfilt; sc[S_THETA0] = theta0; sc[S_ACC] = acc; sc[S_ITERS] = iters + 1;
-        if (trial > 0.0) sc[S_DELTA_LAST] = trial;
-        sc[S_OBJ] = obj; sc[S_ERR] = err0;
-        sc[S_DBG_THT2] = dbg_tht2; sc[S_DBG_AP2] = dbg_ap2;
-        sc[S_DBG_NAN] = dbg_nan; sc[S_DBG_THT0] = dbg_tht0; sc[S_DBG_PHT0] = dbg_pht0; sc[S_DBG_PHI] = phi; sc[S_DBG_SOC] = use_soc;
-        sc[S_DBG_ALPHA] = alpha; sc[S_DBG_AP] = dbg_ap; sc[S_DBG_THETA] = theta; sc[S_DBG_DPHI] = dbg_dphi;
-    }
-}
-
-__device__ void step_part_a(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int lane) {
+// one interior-point iteration of an unfinished instance, in two halves (k_step_a: test, barrier update, factorisation,
+// directions; k_step_b: line search).  `lane` = lane of the warp that runs the scalar logic; g = its group.
+__device__ void step_part_a(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int lane, const Group& g) {
     double* sc = ws.scal(b);
     const int mode = (int)sc[S_MODE];
     if (mode == MODE_DONE) return;
     const int N = pr.N, M = pr.M;
     const Cfg& c = pr.c;
     if (lane == 0) sc[S_PHASE] = PH_NONE;
+    const int rank_for_tick = lane; (void)rank_for_tick;
+    VC_TICK(0);
     const Measures m = finish_gradients(pr, ws, b, lane);
+    VC_TICK(1);
     const bool finite = isfinite(m.f) && isfinite(m.theta) && isfinite(m.rdmax) && isfinite(m.prim);
     double mu = sc[S_MU];
     const double sf = sc[S_SF];
@@ -1397,13 +1351,16 @@ __device__ void step_part_a(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int
     const bool first_ever = delta_last == 0.0;
     double trial = sc[S_DAMP_TRIAL], a_p, a_d, dphi;   // > 0: damped re-solve of this iterate's direction (see k_step_b)
     bool failed = false;
+    VC_TICK(2);
     // ---- inertia-correcting factorisation (IPOPT delta_w ladder) and the slack / multiplier directions
-    while (!riccati(pr, ws, sm, b, lane, mu, trial, false)) {
+    while (!riccati_call(pr, ws, sm, b, g, mu, trial, false)) {
         if (trial == 0.0) trial = first_ever ? 1e-4 : fmax(1e-20, delta_last / 3.0);
         else trial *= first_ever ? 100.0 : 8.0;
         if (trial > 1e40) { failed = true; break; }
     }
+    VC_TICK(4);
     if (!failed) slack_directions(pr, ws, b, lane, mu, tau, false, a_p, a_d, dphi);
+    VC_TICK(5);
     if (lane == 0) {
         sc[S_PHASE] = failed ? PH_FAILED : PH_SEARCH;
         sc[S_MU_NEW] = mu; sc[S_THETA] = theta; sc[S_PHI] = phi; sc[S_THETA0_NEW] = theta0; sc[S_NFILT_NEW] = nfilt;
@@ -1417,7 +1374,7 @@ __device__ void step_part_a(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int
 // k_step_b_wide block (nullptr: evaluate them one after the other)
 struct TrialCache { double ok, f, theta, lns; };
 
-__device__ void step_part_b(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int lane, const TrialCache* cache = nullptr) {
+__device__ void step_part_b(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int lane, const Group& g, const TrialCache* cache = nullptr) {
     double* sc = ws.scal(b);
     const int mode = (int)sc[S_MODE];
     if (mode == MODE_DONE) return;
@@ -1500,7 +1457,7 @@ __device__ void step_part_b(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int
                 soc_residual(pr, ws, b, lane, alpha, false, true);
                 double theta_soc_old = theta;
                 for (int ps = 0; ps < pr.max_soc; ++ps) {
-                    if (!riccati(pr, ws, sm, b, lane, mu, trial, true)) break;
+                    if (!riccati_call(pr, ws, sm, b, g, mu, trial, true)) break;
                     double a_p2, a_d2, dphi2, ft2, tht2, lnt2;
                     slack_directions(pr, ws, b, lane, mu, tau, true, a_p2, a_d2, dphi2);
                     const bool ok2 = trial_point(pr, ws, b, lane, a_p2, true, true, ft2, tht2, lnt2);
@@ -1565,18 +1522,6 @@ __device__ void step_part_b(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int
     }
 }
 
-__global__ void __launch_bounds__(32 * STEP_WARPS, VC_STEP_MINBLOCKS) k_step(Prob pr, Ws ws, int* next_list, int* next_count) {
-    __shared__ WarpSm s_all[STEP_WARPS];
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int i = blockIdx.x * STEP_WARPS + wid;
-    if (i >= *pr.act_count) return;
-    const int b = pr.act_list[i];
-    step_instance(pr, ws, s_all[wid], b, lane);
-    __syncwarp();
-    // survivors form the next pass's compacted list (their order does not influence any instance's result)
-    if (lane == 0 && ws.scal(b)[S_MODE] != (double)MODE_DONE) next_list[atomicAdd(next_count, 1)] = b;
-}
-
 // the two halves of an iteration as separate kernels: the factorisation half needs half the registers of the
 // line-search half (no model code), so it runs at twice the occupancy
 __global__ void __launch_bounds__(32 * STEP_WARPS, 4) k_step_a(Prob pr, Ws ws) {
@@ -1584,7 +1529,7 @@ __global__ void __launch_bounds__(32 * STEP_WARPS, 4) k_step_a(Prob pr, Ws ws) {
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int i = blockIdx.x * STEP_WARPS + wid;
     if (i >= *pr.act_count) return;
-    step_part_a(pr, ws, s_all[wid], pr.act_list[i], lane);
+    step_part_a(pr, ws, s_all[wid], pr.act_list[i], lane, Group{lane, 32, nullptr});
 }
 __global__ void __launch_bounds__(32 * STEP_WARPS, VC_STEP_MINBLOCKS) k_step_b(Prob pr, Ws ws, int* next_list, int* next_count) {
     __shared__ WarpSm s_all[STEP_WARPS];
@@ -1594,22 +1539,39 @@ __global__ void __launch_bounds__(32 * STEP_WARPS, VC_STEP_MINBLOCKS) k_step_b(P
     const int b = pr.act_list[i];
     if (lane == 0) ws.scal(b)[S_UPD_DIR] = 0.0;
     __syncwarp();
-    if (ws.scal(b)[S_MODE] != (double)MODE_DONE) step_part_b(pr, ws, s_all[wid], b, lane);
+    if (ws.scal(b)[S_MODE] != (double)MODE_DONE) step_part_b(pr, ws, s_all[wid], b, lane, Group{lane, 32, nullptr});
     __syncwarp();
     if (lane == 0 && ws.scal(b)[S_MODE] != (double)MODE_DONE) next_list[atomicAdd(next_count, 1)] = b;
 }
 
-// Late passes hold a handful of instances whose line searches backtrack many times, one trial point after the other,
-// on an otherwise idle GPU.  With few instances left a block of LS_TRIALS warps serves ONE instance: warp w evaluates
-// the trial point alpha = a_p 2^-w speculatively, then warp 0 runs the unchanged acceptance logic on the cached values
-// (the first acceptable alpha in the same order: identical results).
+// Late passes hold few instances on an otherwise idle GPU: what counts then is the latency of ONE iteration.  A whole
+// block serves one instance: warp 0 runs the unchanged scalar logic, all warps share the Riccati sweeps (one matrix
+// entry per thread), and in the line-search half warp w evaluates the trial point alpha = a_p 2^-w speculatively
+// before warp 0 applies the unchanged acceptance logic to the cached values (same first acceptable alpha).  Every
+// number is produced by the same arithmetic as in the warp-per-instance kernels: results are identical.
+constexpr int WIDE_A = 128;
+__global__ void __launch_bounds__(WIDE_A, 4) k_step_a_wide(Prob pr, Ws ws) {
+    __shared__ WarpSm s_one;
+    __shared__ GroupCmd s_cmd;
+    if ((int)blockIdx.x >= *pr.act_count) return;
+    const int b = pr.act_list[blockIdx.x];
+    const Group g{(int)threadIdx.x, WIDE_A, &s_cmd};
+    if (threadIdx.x < 32) {
+        step_part_a(pr, ws, s_one, b, threadIdx.x, g);
+        group_release(g);
+    } else {
+        group_helpers(pr, ws, s_one, b, g);
+    }
+}
 constexpr int LS_TRIALS = 12;
 __global__ void __launch_bounds__(32 * LS_TRIALS, 1) k_step_b_wide(Prob pr, Ws ws, int* next_list, int* next_count) {
     __shared__ WarpSm s_one;
+    __shared__ GroupCmd s_cmd;
     __shared__ TrialCache s_trial[LS_TRIALS];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     if ((int)blockIdx.x >= *pr.act_count) return;
     const int b = pr.act_list[blockIdx.x];
+    const Group g{(int)threadIdx.x, 32 * LS_TRIALS, &s_cmd};
     const double* sc = ws.scal(b);
     const bool live = sc[S_MODE] != (double)MODE_DONE;
     const bool search = live && (int)sc[S_PHASE] == PH_SEARCH;
@@ -1621,10 +1583,11 @@ __global__ void __launch_bounds__(32 * LS_TRIALS, 1) k_step_b_wide(Prob pr, Ws w
         if (lane == 0) s_trial[wid] = TrialCache{okv ? 1.0 : 0.0, ft, tht, lnt};
     }
     __syncthreads();
-    if (wid != 0) return;
+    if (wid != 0) { group_helpers(pr, ws, s_one, b, g); return; }
     if (lane == 0) ws.scal(b)[S_UPD_DIR] = 0.0;
     __syncwarp();
-    if (live) step_part_b(pr, ws, s_one, b, lane, search ? s_trial : nullptr);
+    if (live) step_part_b(pr, ws, s_one, b, lane, g, search ? s_trial : nullptr);
+    group_release(g);
     __syncwarp();
     if (lane == 0 && ws.scal(b)[S_MODE] != (double)MODE_DONE) next_list[atomicAdd(next_count, 1)] = b;
 }
@@ -1694,22 +1657,14 @@ static int fill_prob(vc_handle* h, Prob& pr, int B, const double* d_x0, const do
     pr.p = h->params; pr.c = h->cfg;
     pr.B = B; pr.N = h->cfg.N; pr.M = h->cfg.M; pr.H = pr.N + pr.M;
     pr.n_obs = (h->cfg.obstacles && d_obst) ? n_obs : 0;
-    pr.z_init = getenv("VC_ZINIT") ? atof(getenv("VC_ZINIT")) : 0.0;
-    pr.z_cap = getenv("VC_ZCAP") ? atof(getenv("VC_ZCAP")) : 0.0;
-    pr.stall_iters = getenv("VC_STALL") ? atoi(getenv("VC_STALL")) : 4;
-    pr.restore_check = getenv("VC_RESTORE_CHECK") ? atoi(getenv("VC_RESTORE_CHECK")) : 1;
-    pr.max_damp = getenv("VC_MAXDAMP") ? atoi(getenv("VC_MAXDAMP")) : 8;
-    pr.giveup_iters = getenv("VC_GIVEUP") ? atoi(getenv("VC_GIVEUP")) : 24;
-    {   // warm-started solves may enter the monotone barrier ladder a few rungs down: the rungs below are the same
-        // numbers, so the solve ends on the same final rung (and point) as one started at mu_init
-        int rungs = getenv("VC_MU0_RUNGS") ? atoi(getenv("VC_MU0_RUNGS")) : h->cfg.warm_rungs;
+    pr.stall_iters = h->cfg.stall_iters; pr.restore_check = h->cfg.restore_check; pr.max_damp = h->cfg.max_damp;
+    pr.giveup_iters = h->cfg.giveup_iters; pr.max_soc = h->cfg.max_soc; pr.restore_iters = h->cfg.restore_iters;
+    {   // warm-started solves may enter the monotone barrier ladder a few rungs down (option, default off)
         double mu0 = h->cfg.mu_init;
         const double mu_floor = h->cfg.tol / 11.0;
-        for (int i = 0; i < rungs; ++i) mu0 = fmax(mu_floor, fmin(IpmConst::kappa_mu * mu0, pow(mu0, IpmConst::theta_mu)));
+        for (int i = 0; i < h->cfg.warm_rungs; ++i) mu0 = fmax(mu_floor, fmin(IpmConst::kappa_mu * mu0, pow(mu0, IpmConst::theta_mu)));
         pr.mu_start = mu0;
     }
-    pr.max_soc = getenv("VC_MAXSOC") ? atoi(getenv("VC_MAXSOC")) : 4;
-    pr.restore_iters = getenv("VC_RESTORE") ? atoi(getenv("VC_RESTORE")) : 8;
     pr.x0 = d_x0; pr.kappa = d_kappa; pr.ds = d_ds; pr.obst = d_obst;
     pr.X = pr.U = pr.obj = pr.kkt = nullptr; pr.status = pr.iters = nullptr;
     pr.act_list = pr.act_count = nullptr;
@@ -1770,9 +1725,8 @@ int launch_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_k
     const bool debug = getenv("VC_DEBUG") != nullptr;
     int pass = 0;
     const bool prof = h->profiling != 0;
-    const bool split = !(getenv("VC_SPLIT") && atoi(getenv("VC_SPLIT")) == 0);
-    const int wide_max = getenv("VC_WIDE_MAX") ? atoi(getenv("VC_WIDE_MAX")) : 296;   // <= 2 blocks per SM: one instance per block
-    const bool trace = prof && split && getenv("VC_PASS_TRACE") != nullptr;
+    const int wide_max = h->cfg.wide_max;
+    const bool trace = prof && getenv("VC_PASS_TRACE") != nullptr;
     size_t ev = 0;
     auto mark = [&]() {
         if (!prof) return;
@@ -1790,21 +1744,19 @@ int launch_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_k
         if (pr.M > 0) k_eval_pm<<<(unsigned)((t_pm + 127) / 128), 128, 0, st>>>(pr, ws);
         cudaMemsetAsync(counts[1 - cur], 0, sizeof(int), st);
         mark();
-        if (split) {
+        if (n_act <= wide_max) {
+            k_step_a_wide<<<n_act, WIDE_A, 0, st>>>(pr, ws);
+            if (trace) mark();
+            k_step_b_wide<<<n_act, 32 * LS_TRIALS, 0, st>>>(pr, ws, lists[1 - cur], counts[1 - cur]);
+        } else {
             k_step_a<<<(n_act + STEP_WARPS - 1) / STEP_WARPS, 32 * STEP_WARPS, 0, st>>>(pr, ws);
             if (trace) mark();
-            if (n_act <= wide_max)
-                k_step_b_wide<<<n_act, 32 * LS_TRIALS, 0, st>>>(pr, ws, lists[1 - cur], counts[1 - cur]);
-            else
-                k_step_b<<<(n_act + STEP_WARPS - 1) / STEP_WARPS, 32 * STEP_WARPS, 0, st>>>(pr, ws, lists[1 - cur], counts[1 - cur]);
-            k_update<<<(unsigned)(((long long)n_act * pr.H * 32 + 127) / 128), 128, 0, st>>>(pr, ws);
-            h->launches += 2;
-        } else {
-            k_step<<<(n_act + STEP_WARPS - 1) / STEP_WARPS, 32 * STEP_WARPS, 0, st>>>(pr, ws, lists[1 - cur], counts[1 - cur]);
+            k_step_b<<<(n_act + STEP_WARPS - 1) / STEP_WARPS, 32 * STEP_WARPS, 0, st>>>(pr, ws, lists[1 - cur], counts[1 - cur]);
         }
+        k_update<<<(unsigned)(((long long)n_act * pr.H * 32 + 127) / 128), 128, 0, st>>>(pr, ws);
         mark();
         cur = 1 - cur;
-        h->launches += pr.M > 0 ? 3 : 2;
+        h->launches += pr.M > 0 ? 5 : 4;
         if (debug) {   // VC_DEBUG=1: trace instance 0
             double sc[NSCAL];
             cudaMemcpyAsync(sc, ws.scal(0), sizeof(sc), cudaMemcpyDeviceToHost, st);

@@ -42,9 +42,9 @@ def mpc_config_from(cfg, **overrides) -> MpcConfig:
     cw, ic, sc = cfg.cost_weights, cfg.input_constraints, cfg.state_constraints
     pc = cfg.get("state_pm_constraints") or {}
     c = MpcConfig()
+    _capi.load().vc_default_config(C.byref(c))   # IPOPT defaults of the reference (cascaded_mpc.py:55-65) + engine policies
     c.N, c.M = int(cfg.horizon), int(cfg.horizon_pm)
     c.obstacles = 1 if cfg.get("obstacles") else 0
-    c.max_iter = 300
     c.mpc_dt, c.ds_pm = float(cfg.mpc_dt), float(cfg.ds_pm)
     c.w_time, c.w_speed, c.w_ey, c.w_epsi = float(cw.time), float(cw.speed), float(cw.ey), float(cw.epsi)
     c.w_w, c.w_Fx, c.w_Fy = float(cw.w), float(cw.Fx), float(cw.get("Fy", 0.0))
@@ -57,9 +57,9 @@ def mpc_config_from(cfg, **overrides) -> MpcConfig:
     c.ey_min, c.ey_max = float(sc.ey_min), float(sc.ey_max)
     c.V_min = float(pc.get("V_min", sc.Ux_min))
     c.ey_min_pm, c.ey_max_pm = float(pc.get("ey_min", sc.ey_min)), float(pc.get("ey_max", sc.ey_max))
-    # IPOPT defaults the reference runs with (cascaded_mpc.py:55-65)
-    c.tol, c.acceptable_tol, c.acceptable_iter = 1e-8, 1e-6, 15
-    c.obj_scaling, c.mu_init, c.bound_relax = 1, 0.1, 1e-8
+    # solver options may be overridden from the controller yaml ("solver: {max_iter: ..., max_soc: ...}") or by keyword
+    for k, v in dict(cfg.get("solver") or {}).items():
+        setattr(c, k, type(getattr(c, k))(v))
     for k, v in overrides.items():
         setattr(c, k, v)
     return c
