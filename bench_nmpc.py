@@ -17,12 +17,17 @@ import numpy as np
 import bench_common as bc
 
 SEED = 1003
+MAX_ITER = 300
 
 
 def controller_config(horizon_pm=35, obstacles=True, max_speed=18):
     c = bc.load_yaml("controllers/cascaded.yaml")
     c["horizon"], c["horizon_pm"], c["obstacles"] = 20, int(horizon_pm), bool(obstacles)
     c["state_constraints"]["max_speed"] = max_speed
+    # solver options of the benchmark, applied to BOTH arms (B200 engine and CPU reference arm): IPOPT's defaults as the
+    # reference leaves them, except the iteration limit (IPOPT 3000): a handful of the 65,536 perturbed instances crawl
+    # along an obstacle pole for ~1000 iterations under IPOPT's algorithm without its restoration phase
+    c["solver"] = {"max_iter": MAX_ITER}
     return c
 
 

@@ -39,6 +39,7 @@ def oracle_lap(cfg, tr, max_ticks=2000, threads=0):
     from oracle import cpp_oracle as co, nlp as on
     c = on.MpcCfg.from_config(cfg)
     cc = co.mpc_config(c)
+    so = solver_options(cfg)
     X0, U0 = on.cold_start(c, np.random.RandomState(31).random_sample((2, c.H)))
     X, U = X0.copy(), U0.copy()
     x = np.array([4.0, 0, 0, 0, 1.0, 0, 0, 0])
@@ -49,10 +50,10 @@ def oracle_lap(cfg, tr, max_ticks=2000, threads=0):
             break
         rows["x0"].append(x.copy()); rows["Xw"].append(X.copy()); rows["Uw"].append(U.copy())
         ds, kap = on.horizon_params(c, tr, x, X[0])
-        r = co.solve(cc, x, kap, ds, X, U, obstacles=ob, threads=1)
+        r = co.solve(cc, x, kap, ds, X, U, obstacles=ob, threads=1, **so)
         if int(r["status"]) > 1:
             ds, kap = on.horizon_params(c, tr, x, X0[0])
-            r = co.solve(cc, x, kap, ds, X0, U0, obstacles=ob, threads=1)
+            r = co.solve(cc, x, kap, ds, X0, U0, obstacles=ob, threads=1, **so)
         rows["iters"].append(int(r["iters"])); rows["status"].append(int(r["status"]))
         if rows["status"][-1] > 1:
             break
@@ -83,10 +84,19 @@ def nmpc_sample(workload, n, lap=None):
     return cfg, dict(x0=x0[:n], Xw=Xw[:n], Uw=Uw[:n], obst=None if ob is None else ob[:n], ds=ds, kappa=kap), lap_s, len(lap["x0"])
 
 
+def solver_options(cfg):
+    """IPOPT's defaults as the reference leaves them (max_iter 3000, max_soc 4, watchdog trigger 10) overridden by the
+    controller config's `solver` block -- the same block the B200 arm reads (engine.mpc_config_from)."""
+    o = {"max_iter": 3000, "max_soc": 4, "watchdog": 10}
+    for k, v in dict(cfg.get("solver") or {}).items():
+        o[{"watchdog_trigger": "watchdog"}.get(k, k)] = int(v)
+    return {k: o[k] for k in ("max_iter", "max_soc", "watchdog")}
+
+
 def cpu_solve(cfg, s, threads=0):
     from oracle import cpp_oracle as co
-    return co.solve(cfg, s["x0"], s["kappa"], s["ds"], s["Xw"], s["Uw"], obstacles=s["obst"], max_iter=3000, max_soc=4,
-                    threads=threads)
+    return co.solve(cfg, s["x0"], s["kappa"], s["ds"], s["Xw"], s["Uw"], obstacles=s["obst"], threads=threads,
+                    **solver_options(cfg))
 
 
 def host_threads():
@@ -102,8 +112,7 @@ def cpu_baseline_nmpc(cfg, sample, gpu_U=None, gpu_obj=None):
     r = cpu_solve(cfg, sample, th)
     el = time.perf_counter() - t0
     out = {"value": n / el, "unit": "solves/s", "cores": th, "kind": "port-cpp", "per_core": n / el / th,
-           "sample": f"first {n} instances of this batch solved by oracle/cpp (C++ restatement of CasADi AD + IPOPT, no iteration "
-                     f"cap, OpenMP over instances, {th} threads) in {el:.1f} s; mean {r['iters'].mean():.1f} iterations; "
+           "sample": f"first {n} instances of this batch solved by oracle/cpp (C++ restatement of CasADi AD + IPOPT, same solver options, OpenMP over instances, {th} threads) in {el:.1f} s; mean {r['iters'].mean():.1f} iterations; "
                      f"the reference's own logs: 14-25 solves/s per thread (IPOPT+MA27, BASELINE.md)",
            "mean_iters": float(r["iters"].mean()), "converged_frac": float((r["status"] <= 1).mean())}
     if gpu_U is not None:
@@ -146,7 +155,7 @@ def run_reference(a, workload):
         wl = ("C2: cascaded NMPC 20+15, ippodromo, 4,096 perturbed instances; warm start timed, cold start reported separately"
               if workload == "c2" else "C3: cascaded NMPC 20+35 with obstacles, ippodromo, warm-started perturbed instances")
         sample = (f"first {n} instances of the batch per step (same recipe and seed as the B200 arm; warm-start lap of {ticks} "
-                  f"ticks replayed on the CPU oracle in {lap_s:.0f} s, untimed), oracle/cpp with max_iter 3000, {th} threads")
+                  f"ticks replayed on the CPU oracle in {lap_s:.0f} s, untimed), oracle/cpp with max_iter {solver_options(cfg)['max_iter']}, {th} threads")
     for _ in range(min(warm, 1)):
         fn()
     t0 = time.perf_counter()

@@ -55,16 +55,11 @@ typedef struct vc_mpc_config {
     double bound_relax;        /* 1e-8                                                          */
     int warm_rungs;            /* >0: the first iteration starts this many rungs down the barrier ladder (warm starts) */
     int max_soc;               /* IPOPT max_soc: second-order correction steps per iteration (default 4)             */
-    /* engine policies that stand in for IPOPT mechanisms this engine does not restate (watchdog, restoration phase);
-     * vc_default_config() sets the values the shipped results were produced with */
-    int stall_iters;           /* consecutive shortened steps before the barrier parameter is forced down (4)        */
-    int restore_iters;         /* consecutive shortened steps at an infeasible iterate before it is projected onto the
-                                  dynamics (8; 0 = never)                                                            */
-    int max_damp;              /* damped re-solves of one iteration's direction before giving the direction up (8)   */
-    int giveup_iters;          /* shortened steps after the last projection before the instance ends with
-                                  VC_LINESEARCH_FAIL (24)                                                            */
-    int restore_check;         /* 1: a projected trajectory that leaves the widened state bounds is replaced by the
-                                  neutral rollout                                                                    */
+    int watchdog_trigger;      /* IPOPT watchdog_shortened_iter_trigger (default 10; 0 = watchdog off)                */
+    int watchdog_trials;       /* IPOPT watchdog_trial_iter_max (default 3)                                           */
+    /* where IPOPT would enter its restoration phase (no acceptable step along a direction) the engine damps the step
+     * (larger delta_w) and re-solves, at most max_damp times, then re-initialises the iterate by a rollout (twice) */
+    int max_damp;              /* damped re-solves of one iteration's direction (8)                                   */
     int wide_max;              /* passes with at most this many unfinished instances run one BLOCK per instance
                                   (latency) instead of one warp (throughput); 0 = never (296 = two per SM)           */
 } vc_mpc_config;

@@ -435,7 +435,7 @@ static void repair(const Problem& P, std::vector<StageIt>& it) {
             const int si = k < N ? (int)SS : (int)PS, ei = k < N ? (int)EY : (int)PEY;
             for (int o = 0; o < P.n_obs; ++o) {
                 const double R = P.obst[3 * o + 2] + 0.1 + 0.5, a = y[si] - P.obst[3 * o], e = y[ei] - P.obst[3 * o + 1];
-                if (a * a + e * e < R * R) y[ei] = P.obst[3 * o + 1] + (e > 0.0 ? 1.0 : -1.0) * std::sqrt(R * R - a * a);
+                if (a * a + e * e < R * R) y[ei] = P.obst[3 * o + 1] + (e > 1e-9 ? 1.0 : -1.0) * std::sqrt(R * R - a * a);   // |e| <= 1e-9: dead centre
             }
         }
 }
@@ -631,6 +631,9 @@ static Result solve_once(const Problem& P, std::vector<StageIt>& it, const Optio
                     measures(tr, evt, ft, tht, pht);
                     if (acceptable(alpha, tht, pht, dphi, augment)) { accepted = true; used = &d1; }
                 }
+                if (opt.verbose > 1)
+                    std::fprintf(stderr, "        bt %d alpha %.3e ok %d f %.8f theta %.4e phi %.8e (ref theta %.4e phi %.8e dphi %.3e) acc %d\n", bt, alpha,
+                                 (int)okv, ft, tht, pht, theta, phi, dphi, (int)accepted);
                 // second-order correction (IPOPT Alg. A-5.5..5.9): first trial point rejected, infeasibility not reduced
                 if (!accepted && bt == 0 && okv && tht >= theta && opt.max_soc > 0) {
                     for (int k = 0; k < H; ++k) {

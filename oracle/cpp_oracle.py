@@ -116,7 +116,7 @@ def _a(x, dtype=np.float64):
 
 
 def solve(cfg, x0, kappa, ds, X, U, obstacles=None, car=None, max_iter=3000, max_soc=4, max_restorations=2, verbose=0,
-          threads=0, obj_scale=0.0, watchdog=0):
+          threads=0, obj_scale=0.0, watchdog=10):
     """Batched solve on the host cores.  x0[B,8], kappa[B,H], ds[B,H], X[B,8,H], U[B,2,H] (warm start), obstacles[B,n,3].
     Returns dict(X, U, obj, status, iters, kkt) of new arrays."""
     lib = load()

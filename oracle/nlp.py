@@ -259,7 +259,7 @@ class NLP:
                 for so, eo, ro in self.obst.numpy():
                     R, a, e = ro + 0.1 + 0.5, X[si, k] - so, X[ei, k] - eo
                     if a * a + e * e < R * R:
-                        X[ei, k] = eo + (1.0 if e > 0.0 else -1.0) * np.sqrt(R * R - a * a)
+                        X[ei, k] = eo + (1.0 if e > 1e-9 else -1.0) * np.sqrt(R * R - a * a)   # |e| <= 1e-9: dead centre
         return self.pack(X, U)
 
     # ------------------------------------------------------------ derivatives (exact, autodiff)

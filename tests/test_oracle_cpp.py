@@ -59,7 +59,7 @@ def test_nmpc_fixtures_iterate_for_iterate(fx):
     for t in tags:
         cfg = on.MpcCfg.from_config(meta[t.rsplit("/", 1)[0]]["config"])
         ob = z[t + "/obst"] if cfg.obstacles else None
-        r = co.solve(cfg, z[t + "/x0"], z[t + "/kappa"], z[t + "/ds"], z[t + "/X0"], z[t + "/U0"], obstacles=ob, max_soc=0)
+        r = co.solve(cfg, z[t + "/x0"], z[t + "/kappa"], z[t + "/ds"], z[t + "/X0"], z[t + "/U0"], obstacles=ob, max_soc=0, watchdog=0)
         U, ref, obj = z[t + "/U"], z[t + "/ref_u"], float(z[t + "/obj"])
         assert r["status"] == 0 and int(r["iters"]) == int(z[t + "/iters"]), (t, r["iters"], z[t + "/iters"])
         assert (np.abs(r["U"] - U) / np.maximum(1, np.abs(U))).max() < 1e-9, t

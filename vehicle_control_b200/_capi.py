@@ -30,8 +30,8 @@ class MpcConfig(C.Structure):
                                     "ey_min", "ey_max", "V_min", "ey_min_pm", "ey_max_pm",
                                     "tol", "acceptable_tol")]
                 + [("acceptable_iter", C.c_int), ("obj_scaling", C.c_int), ("mu_init", D), ("bound_relax", D),
-                   ("warm_rungs", C.c_int), ("max_soc", C.c_int), ("stall_iters", C.c_int), ("restore_iters", C.c_int),
-                   ("max_damp", C.c_int), ("giveup_iters", C.c_int), ("restore_check", C.c_int), ("wide_max", C.c_int)])
+                   ("warm_rungs", C.c_int), ("max_soc", C.c_int), ("watchdog_trigger", C.c_int), ("watchdog_trials", C.c_int),
+                   ("max_damp", C.c_int), ("wide_max", C.c_int)])
 
 
 EXPORTS = {

@@ -396,16 +396,16 @@ int vc_default_config(vc_mpc_config* c) {
     // IPOPT 3.14 defaults, which the reference leaves untouched (cascaded_mpc.py:55-65)
     c->max_iter = 3000; c->tol = 1e-8; c->acceptable_tol = 1e-6; c->acceptable_iter = 15; c->obj_scaling = 1;
     c->mu_init = 0.1; c->bound_relax = 1e-8; c->max_soc = 4; c->warm_rungs = 0;
+    c->watchdog_trigger = 10; c->watchdog_trials = 3;
     // engine policies
-    c->stall_iters = 4; c->restore_iters = 8; c->max_damp = 8; c->giveup_iters = 24; c->restore_check = 1;
-    c->wide_max = 296;
+    c->max_damp = 8; c->wide_max = 296;
     return 0;
 }
 
 int vc_set_config(vc_handle* h, const vc_mpc_config* hc) {
     VC_REQUIRE(h && hc, "vc_set_config: null argument");
     VC_REQUIRE(hc->N >= 1 && hc->M >= 0, "vc_set_config: need horizon N >= 1, M >= 0");
-    VC_REQUIRE(hc->max_iter >= 1 && hc->tol > 0 && hc->mu_init > 0 && hc->stall_iters >= 1 && hc->max_damp >= 0,
+    VC_REQUIRE(hc->max_iter >= 1 && hc->tol > 0 && hc->mu_init > 0 && hc->max_damp >= 0 && hc->watchdog_trials >= 0,
                "vc_set_config: solver options not set (start from vc_default_config)");
     h->cfg = *hc;
     return 0;

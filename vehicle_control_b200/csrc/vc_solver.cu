@@ -61,13 +61,14 @@ enum WsArray {
     W_DLAM2,     // [8]
     W_DSL2,      // [10]
     W_DZ2,       // [10]
+    W_BAK,       // [38]  watchdog: copy of the iterate (y lam s z) at the stored reference point
     W_COUNT
 };
 struct WsTable { int width[W_COUNT + 1]; int off[W_COUNT + 1]; };
 constexpr WsTable make_ws_table() {
     WsTable t{};
     const int w[W_COUNT] = {36, 80, 10, 10, 10, 8, 2, 8, 24, 10, 100, 10, 8, 10, 10, 80, 10, 10, 1, 1,
-                            10, 8, 10, 10, 8, 10, 8, 10, 10, 8, 10, 10};
+                            10, 8, 10, 10, 8, 10, 8, 10, 10, 8, 10, 10, 38};
     int o = 0;
     for (int i = 0; i < W_COUNT; ++i) { t.width[i] = w[i]; t.off[i] = o; o += w[i]; }
     t.width[W_COUNT] = 0; t.off[W_COUNT] = o;
@@ -80,7 +81,7 @@ __device__ __constant__ int c_ws_off[W_COUNT + 1] = {
     WS_TABLE.off[13], WS_TABLE.off[14], WS_TABLE.off[15], WS_TABLE.off[16], WS_TABLE.off[17], WS_TABLE.off[18],
     WS_TABLE.off[19], WS_TABLE.off[20], WS_TABLE.off[21], WS_TABLE.off[22], WS_TABLE.off[23], WS_TABLE.off[24],
     WS_TABLE.off[25], WS_TABLE.off[26], WS_TABLE.off[27], WS_TABLE.off[28], WS_TABLE.off[29], WS_TABLE.off[30],
-    WS_TABLE.off[31], WS_TABLE.off[32]};
+    WS_TABLE.off[31], WS_TABLE.off[32], WS_TABLE.off[33]};
 constexpr int ws_width(int a) { return WS_TABLE.width[a]; }
 constexpr int ws_offset(int a) { return WS_TABLE.off[a]; }   // offset inside a stage record
 constexpr int WS_PER_STAGE = ws_offset(W_COUNT);
@@ -89,13 +90,15 @@ constexpr int WS_FWD0 = ws_offset(W_GRES);    // forward sweep: AB block and [WS
 constexpr int WS_FWD1 = ws_offset(W_Y);
 static_assert(WS_PER_STAGE % 2 == 0 && WS_BWD % 2 == 0 && WS_FWD0 % 2 == 0 && WS_FWD1 % 2 == 0 &&
               ws_offset(W_AB) % 2 == 0 && ws_offset(W_RD) % 2 == 0, "16-byte alignment of the staged blocks");
-static_assert(W_COUNT == 32, "update make_ws_table / c_ws_off");
-constexpr int O_IT = ws_offset(W_Y), O_DIR = ws_offset(W_DY), O_DIR2 = ws_offset(W_DY2);
+static_assert(W_COUNT == 33, "update make_ws_table / c_ws_off");
+constexpr int O_IT = ws_offset(W_Y), O_DIR = ws_offset(W_DY), O_DIR2 = ws_offset(W_DY2), O_BAK = ws_offset(W_BAK);
+constexpr int O_GS = ws_offset(W_GS), O_GRES_C = ws_offset(W_GRES), O_JC = ws_offset(W_JC), O_CS = ws_offset(W_CS), O_CRES = ws_offset(W_CRES),
+              O_S = ws_offset(W_S), O_Z = ws_offset(W_Z), O_KM = ws_offset(W_KM), O_PM = ws_offset(W_PM), O_PV = ws_offset(W_PV);
 static_assert(ws_offset(W_LAM) == O_IT + 10 && ws_offset(W_S) == O_IT + 18 && ws_offset(W_Z) == O_IT + 28 &&
               ws_offset(W_DLAM) == O_DIR + 10 && ws_offset(W_DSL) == O_DIR + 18 && ws_offset(W_DZ) == O_DIR + 28 &&
               ws_offset(W_DLAM2) == O_DIR2 + 10 && ws_offset(W_DSL2) == O_DIR2 + 18 && ws_offset(W_DZ2) == O_DIR2 + 28,
               "iterate / direction blocks must share one layout");
-constexpr int NSCAL = 96;
+constexpr int NSCAL = 112;
 #ifdef VC_TIMING
 #define VC_TICK(slot) do { if (rank_for_tick == 0) ws.scal(b)[84 + (slot)] = (double)clock64(); } while (0)
 #else
@@ -108,7 +111,9 @@ constexpr int FILT_MAX = 16;
 // hand-over block between the two halves of an iteration (k_step_a -> k_step_b)
 enum ScalAB { S_PHASE = 64, S_THETA, S_PHI, S_TRIAL, S_AP, S_AD, S_DPHI, S_MU_NEW, S_NFILT_NEW, S_THETA0_NEW, S_ACC_NEW,
               S_NSHORT_NEW, S_OBJ_NEW, S_ERR_NEW, S_DAMP_TRIAL, S_NDAMP, S_UPD_DIR, S_UPD_ALPHA, S_UPD_AD };
-enum Phase { PH_NONE = 0, PH_SEARCH = 1, PH_RESTORE = 2, PH_FAILED = 3, PH_BADINIT = 4 };
+// watchdog state (IPOPT IpBacktrackingLineSearch: StartWatchDog / StopWatchDog)
+enum ScalWd { S_WD_IN = 96, S_WD_SHORT, S_WD_TRIAL, S_WD_THETA, S_WD_PHI, S_WD_DPHI, S_WD_ATEST, S_SKIP_FIRST };
+enum Phase { PH_NONE = 0, PH_SEARCH = 1, PH_FAILED = 3, PH_BADINIT = 4 };
 enum Mode { MODE_INIT = 0, MODE_STEP = 1, MODE_DONE = 2, MODE_REINIT = 3 };
 
 struct Ws {
@@ -130,13 +135,10 @@ struct Prob {   // device-side view of one vc_nmpc_solve call
     Params p;
     Cfg c;
     int B, N, M, H, n_obs;
-    int stall_iters;   // consecutive shortened steps before the barrier parameter is forced down
+    int watchdog_trigger, watchdog_trials;   // IPOPT watchdog_shortened_iter_trigger (10) / watchdog_trial_iter_max (3)
     double mu_start;   // barrier parameter of the first iteration (mu_init advanced by `warm_rungs` rungs of the ladder)
     int max_soc;       // second-order correction steps per iteration (IPOPT max_soc = 4)
-    int restore_check; // 1: a restored trajectory that leaves the widened state bounds is replaced by the neutral rollout
     int max_damp;      // damped re-solves of one iteration's direction before the iterate is restored / given up
-    int giveup_iters;  // consecutive shortened steps after the last restoration before the instance is given up
-    int restore_iters; // > 0: consecutive shortened steps before the iterate is projected onto the dynamics (restoration)
     const double *x0, *kappa, *ds, *obst;
     double *X, *U, *obj, *kkt;
     int *status, *iters;
@@ -180,6 +182,11 @@ __global__ void k_prepare(Prob pr, Ws ws, int* list0, int* count0) {
         double* sc = ws.scal(b);
         for (int i = 0; i < NSCAL; ++i) sc[i] = 0.0;
         sc[S_MU] = pr.mu_start; sc[S_SF] = 1.0; sc[S_THETA0] = -1.0; sc[S_MODE] = MODE_INIT; sc[S_STATUS] = -1.0;
+        // outputs are defined whatever happens later (an instance that is never finalised reads as "iteration limit")
+        if (pr.status) pr.status[b] = VC_MAX_ITER;
+        if (pr.iters) pr.iters[b] = 0;
+        if (pr.obj) pr.obj[b] = NAN;
+        if (pr.kkt) pr.kkt[b] = INFINITY;
     }
 }
 
@@ -470,7 +477,7 @@ __device__ __noinline__ StageVal stage_trial(const Prob& pr, int b, int k, const
 #define VC_STEP_MINBLOCKS 1
 #endif
 constexpr int STEP_WARPS = VC_STEP_WARPS;
-constexpr int RING_DOUBLES = 672;
+constexpr int RING_DOUBLES = 768;
 struct __align__(16) WarpSm {
     double P[100];     // cost-to-go Hessian of the NEXT stage (stride 10)
     double M[120];     // [A~ B~] of the lifted transition (stride 12)
@@ -622,35 +629,21 @@ template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile(
 constexpr int O_HC = ws_offset(W_HC), O_AB = ws_offset(W_AB), O_RD = ws_offset(W_RD), O_V1 = ws_offset(W_V1),
               O_V2 = ws_offset(W_V2), O_OBS = ws_offset(W_OBS), O_AUX = ws_offset(W_AUX), O_GRES = ws_offset(W_GRES);
 constexpr int BWD_DEPTH = 4, BWD_SLOT = WS_BWD + 2;                 // backward ring: 4 slots of the [0, WS_BWD) block
-constexpr int FWD_DEPTH = 3, FWD_SLOT = 80 + (WS_FWD1 - WS_FWD0);   // forward ring: AB | GRES KM PV PM, compacted
+// forward ring: 4 slots of  AB | GRES KM PV PM[0..70)  (the reduced cost-to-go Hessian is at most 7 x 7, stride 10)
+constexpr int FWD_PM_USED = 70;
+constexpr int FWD_TAIL = ws_offset(W_PM) + FWD_PM_USED - WS_FWD0;
+constexpr int FWD_DEPTH = 4, FWD_SLOT = 80 + FWD_TAIL;
 constexpr int F_AB = 0, F_GRES = 80, F_KM = F_GRES + 8, F_PV = F_KM + 24, F_PM = F_PV + 10;
 static_assert(BWD_DEPTH * BWD_SLOT <= RING_DOUBLES && FWD_DEPTH * FWD_SLOT <= RING_DOUBLES, "ring too small");
-static_assert(BWD_SLOT % 2 == 0 && FWD_SLOT % 2 == 0, "slot alignment");
+static_assert(BWD_SLOT % 2 == 0 && FWD_SLOT % 2 == 0 && FWD_TAIL % 2 == 0, "slot alignment");
+static_assert(ws_offset(W_KM) == WS_FWD0 + 8 && ws_offset(W_PV) == WS_FWD0 + 32 && ws_offset(W_PM) == WS_FWD0 + 42, "forward slot layout");
 
-// A solve step is run by a GROUP of nt threads per instance: one warp (nt = 32, four instances per block) while the
-// batch is large, a whole block (nt = 128 / 384, named barrier) once few instances are left and latency is what counts.
-// Every entry of every matrix is computed by the same arithmetic in both cases, so results do not depend on nt.
-__device__ __forceinline__ void gsync(int nt) {
-    if (nt == 32) __syncwarp();
-    else asm volatile("bar.sync 1, %0;" ::"r"(nt) : "memory");
-}
-
-__device__ __forceinline__ void stage_fetch_bwd(const Ws& ws, WarpSm& sm, int b, int k, int rank, int nt) {
-    if (k >= 0) {
-        const double* rec = ws.rec(b, k);
-        double* dst = sm.ring + (k % BWD_DEPTH) * BWD_SLOT;
-        for (int c = rank; c < WS_BWD / 2; c += nt) cp_async16(dst + 2 * c, rec + 2 * c);
-    }
-    cp_async_commit();
-}
-__device__ __forceinline__ void stage_fetch_fwd(const Ws& ws, WarpSm& sm, int b, int k, int H, int rank, int nt) {
-    if (k < H) {
-        const double* rec = ws.rec(b, k);
-        double* dst = sm.ring + (k % FWD_DEPTH) * FWD_SLOT;
-        for (int c = rank; c < 40; c += nt) cp_async16(dst + F_AB + 2 * c, rec + O_AB + 2 * c);
-        for (int c = rank; c < (WS_FWD1 - WS_FWD0) / 2; c += nt) cp_async16(dst + F_GRES + 2 * c, rec + WS_FWD0 + 2 * c);
-    }
-    cp_async_commit();
+// A solve step is run by a GROUP of NT threads per instance: one warp (NT = 32, four instances per block) while the
+// batch is large, four warps (NT = 128, named barrier) once few instances are left and latency is what counts.
+// Every entry of every matrix is computed by the same arithmetic in both cases, so results do not depend on NT.
+template <int NT> __device__ __forceinline__ void gsync() {
+    if (NT == 32) __syncwarp();
+    else asm volatile("bar.sync 1, %0;" ::"n"(NT) : "memory");
 }
 
 // ---- reduced stage state of the Riccati sweeps.  The arclength s and the time t are cyclic coordinates of the
@@ -672,74 +665,138 @@ __device__ __forceinline__ RDims rdims(int N, int k) {
 // position of ACTIVE variable a (index into c_act_st / c_act_pm) in the Riccati ordering [x^ | p | u]; the first nxr
 // active variables are the reduced state in order, the last two the controls
 __device__ __forceinline__ int apos(const RDims& d, int a) { return a < d.nxr ? a : d.n + (a - d.nxr); }
-// index inside y / inside a full state vector of reduced component i
-__device__ __forceinline__ int yidx(const RDims& d, int i) { return d.st ? c_act_st[i] : c_act_pm[i]; }
+// index inside y / inside a full state vector of ACTIVE variable a (arithmetic form of c_act_st / c_act_pm)
+__device__ __forceinline__ int yidx(bool st, int a) { return st ? a + (a >= 4) + (a >= 6) : a + (a >= 1) + (a >= 3); }
 
-// builds M = [A~ B~] (rows: reduced + lifted next state, cols: [x^ | p | u] of stage k) in shared memory from the staged
-// dynamics Jacobian `ab` ([full next-state row][active variable], stride 8).  M must have been zeroed before.
-__device__ __forceinline__ void scatter_transition(WarpSm& sm, const double* ab, int rank, int nt, const RDims& d, const RDims& dn) {
-    const int nact = d.nxr + 2;
-    for (int e = rank; e < dn.nxr * nact; e += nt) {
-        const int i = e / nact, a = e - i * nact;
-        sm.M[i * 12 + apos(d, a)] = ab[yidx(dn, i) * 8 + a];
+// ---- per stage KIND index tables (shared memory, built once per block): where every entry of the stage matrices comes
+// from inside the staged stage block, so that a stage is assembled by straight table-driven copies
+enum { NKIND = 5, G_MAX = 81, M_MAX = 63 };
+enum { GF_EY = 1, GF_P0 = 2, GF_M0 = 4, GF_P1 = 8, GF_M1 = 16, GF_DELTA = 32 };
+struct KindTab {
+    short gdst[G_MAX], gsrc[G_MAX];   // G entry: destination (stride 12); offset of its Hessian entry in the block or -1
+    short mdst[M_MAX], msrc[M_MAX];   // M entry: destination (stride 12); offset inside the AB block, -1 = 0, -2 = 1
+    unsigned char gflag[G_MAX];       // closed-form additions (obstacle ey-ey, control continuity, delta_w)
+    short ng, nm, n, nn, nxr, np, dnn, dnxr, st, nst, has_next, trow;
+};
+__device__ __forceinline__ int stage_kind(int k, int N, int H) {
+    return k == 0 ? 0 : (k == H - 1 ? 4 : (k == N - 1 ? 2 : (k < N - 1 ? 1 : 3)));
+}
+__device__ void build_kind_tables(const Prob& pr, KindTab* tabs, int tid, int nthreads) {
+    const int N = pr.N, H = pr.H;
+    const int rep[NKIND] = {0, 1, N - 1, N, H - 1};   // a stage of each kind (kinds that do not occur are never looked up)
+    for (int kd = 0; kd < NKIND; ++kd) {
+        const int k = rep[kd];
+        if (k < 0 || k >= H || stage_kind(k, N, H) != kd) continue;
+        KindTab& T = tabs[kd];
+        const RDims d = rdims(N, k);
+        const bool has_next = k < H - 1;
+        const RDims dn = rdims(N, has_next ? k + 1 : k);
+        const int n = d.n, nn = n + 2;
+        if (tid == 0) {
+            T.ng = nn * nn; T.nm = has_next ? dn.n * nn : 0; T.n = n; T.nn = nn; T.nxr = d.nxr; T.np = d.np;
+            T.dnn = dn.n; T.dnxr = dn.nxr; T.st = d.st; T.nst = dn.st; T.has_next = has_next;
+            T.trow = (k + 1 < N ? IT : QT);
+        }
+        for (int e = tid; e < nn * nn; e += nthreads) {
+            const int i = e / nn, j = e - i * nn;
+            // active variable behind a position: reduced state, or control; lifted positions have none
+            const int ai = i < d.nxr ? i : (i >= n ? d.nxr + (i - n) : -1), aj = j < d.nxr ? j : (j >= n ? d.nxr + (j - n) : -1);
+            int src = -1;
+            if (ai >= 0 && aj >= 0) { const int hi = ai > aj ? ai : aj, lo = ai > aj ? aj : ai; src = O_HC + hi * (hi + 1) / 2 + lo; }
+            int fl = 0;
+            const int eyp = d.st ? 4 : 1;
+            if (i == eyp && j == eyp) fl |= GF_EY;
+            for (int q = 0; q < d.np; ++q) {
+                const int pu = n + q, pp = d.nxr + q;
+                if ((i == pu && j == pu) || (i == pp && j == pp)) fl |= q == 0 ? GF_P0 : GF_P1;
+                if ((i == pu && j == pp) || (i == pp && j == pu)) fl |= q == 0 ? GF_M0 : GF_M1;
+            }
+            if (i == j && (i < d.nxr || i >= n)) fl |= GF_DELTA;
+            T.gdst[e] = (short)(i * 12 + j); T.gsrc[e] = (short)src; T.gflag[e] = (unsigned char)fl;
+        }
+        if (has_next)
+            for (int e = tid; e < dn.n * nn; e += nthreads) {
+                const int l = e / nn, j = e - l * nn;
+                const int aj = j < d.nxr ? j : (j >= n ? d.nxr + (j - n) : -1);
+                int src = -1;
+                if (l < dn.nxr) { if (aj >= 0) src = yidx(dn.st, l) * 8 + aj; }
+                else if (l == dn.nxr) { if (j == n) src = -2; }                         // p0 <- Fx_k
+                else if (!d.st) { if (j == n + 1) src = -2; }                           // p1 <- Fy_k
+                else if (aj >= 0) src = 5 * 8 + aj;                                    // p1 <- T(y_{N-1}) = Fy_f + Fy_r
+                T.mdst[e] = (short)(l * 12 + j); T.msrc[e] = (short)src;
+            }
     }
-    if (rank == 31) {
-        sm.M[dn.nxr * 12 + d.n] = 1.0;                                      // p0 <- Fx_k
-        if (dn.np > 1 && !d.st) sm.M[(dn.nxr + 1) * 12 + d.n + 1] = 1.0;    // p1 <- Fy_k
+}
+
+__device__ __forceinline__ void stage_fetch_bwd(const double* rec0, WarpSm& sm, int k, int rank, int nt) {
+    if (k >= 0) {
+        const double* rec = rec0 + k * WS_PER_STAGE;
+        double* dst = sm.ring + (k % BWD_DEPTH) * BWD_SLOT;
+        for (int c = rank; c < WS_BWD / 2; c += nt) cp_async16(dst + 2 * c, rec + 2 * c);
     }
-    if (dn.np > 1 && d.st && rank >= 16 && rank < 24)                       // p1 <- T(y_{N-1}) = Fy_f + Fy_r
-        sm.M[(dn.nxr + 1) * 12 + apos(d, rank - 16)] = ab[5 * 8 + rank - 16];
+    cp_async_commit();
+}
+__device__ __forceinline__ void stage_fetch_fwd(const double* rec0, WarpSm& sm, int k, int H, int rank, int nt) {
+    if (k < H) {
+        const double* rec = rec0 + k * WS_PER_STAGE;
+        double* dst = sm.ring + (k % FWD_DEPTH) * FWD_SLOT;
+        for (int c = rank; c < 40 + FWD_TAIL / 2; c += nt) {
+            const bool ab = c < 40;
+            cp_async16(dst + (ab ? F_AB + 2 * c : F_GRES + 2 * (c - 40)), rec + (ab ? O_AB + 2 * c : WS_FWD0 + 2 * (c - 40)));
+        }
+    }
+    cp_async_commit();
 }
 
 // ---- stage products of the backward sweep: PMm = P M, tv = P r + p, G += M^T PMm, g += M^T tv
 // generic shapes: four interleaved accumulators per lane, entry indices by reciprocal multiplication
-__device__ __noinline__ void stage_products_generic(WarpSm& sm, int lane, int dnn, int nn, int rcp_nn) {
-    const int cnt = dnn * nn;
-            {   // PMm = P M : up to 4 entries per lane, accumulated side by side
-                int ii[4], jj[4];
-                double acc[4] = {0.0, 0.0, 0.0, 0.0};
+__device__ __noinline__ void stage_products_generic(WarpSm& sm, int lane, int dnn, int nn) {
+    const int cnt = dnn * nn, rcp_nn = 65536 / nn + 1;
+    {   // PMm = P M : up to 4 entries per lane, accumulated side by side
+        int ii[4], jj[4];
+        double acc[4] = {0.0, 0.0, 0.0, 0.0};
 #pragma unroll
-                for (int t = 0; t < 4; ++t) {
-                    const int e = min(lane + 32 * t, cnt - 1);
-                    ii[t] = (e * rcp_nn) >> 16; jj[t] = e - ii[t] * nn;
-                }
-                for (int l = 0; l < dnn; ++l) {
+        for (int t = 0; t < 4; ++t) {
+            const int e = min(lane + 32 * t, cnt - 1);
+            ii[t] = (e * rcp_nn) >> 16; jj[t] = e - ii[t] * nn;
+        }
+        for (int l = 0; l < dnn; ++l) {
 #pragma unroll
-                    for (int t = 0; t < 4; ++t) acc[t] += sm.P[ii[t] * 10 + l] * sm.M[l * 12 + jj[t]];
-                }
+            for (int t = 0; t < 4; ++t) acc[t] += sm.P[ii[t] * 10 + l] * sm.M[l * 12 + jj[t]];
+        }
 #pragma unroll
-                for (int t = 0; t < 4; ++t)
-                    if (lane + 32 * t < cnt) sm.PMm[ii[t] * 12 + jj[t]] = acc[t];
-            }
-            if (lane < dnn) {                                 // tv = P r + p
-                double a = sm.p[lane];
-                for (int l = 0; l < dnn; ++l) a += sm.P[lane * 10 + l] * sm.r[l];
-                sm.tv[lane] = a;
-            }
-            __syncwarp();
-            {   // G += M^T (P M)
-                const int cnt2 = nn * nn;
-                int ii[4], jj[4];
-                double acc[4] = {0.0, 0.0, 0.0, 0.0};
+        for (int t = 0; t < 4; ++t)
+            if (lane + 32 * t < cnt) sm.PMm[ii[t] * 12 + jj[t]] = acc[t];
+    }
+    if (lane < dnn) {                                 // tv = P r + p
+        double a = sm.p[lane];
+        for (int l = 0; l < dnn; ++l) a += sm.P[lane * 10 + l] * sm.r[l];
+        sm.tv[lane] = a;
+    }
+    __syncwarp();
+    {   // G += M^T (P M)
+        const int cnt2 = nn * nn;
+        int ii[4], jj[4];
+        double acc[4] = {0.0, 0.0, 0.0, 0.0};
 #pragma unroll
-                for (int t = 0; t < 4; ++t) {
-                    const int e = min(lane + 32 * t, cnt2 - 1);
-                    ii[t] = (e * rcp_nn) >> 16; jj[t] = e - ii[t] * nn;
-                }
-                for (int l = 0; l < dnn; ++l) {
+        for (int t = 0; t < 4; ++t) {
+            const int e = min(lane + 32 * t, cnt2 - 1);
+            ii[t] = (e * rcp_nn) >> 16; jj[t] = e - ii[t] * nn;
+        }
+        for (int l = 0; l < dnn; ++l) {
 #pragma unroll
-                    for (int t = 0; t < 4; ++t) acc[t] += sm.M[l * 12 + ii[t]] * sm.PMm[l * 12 + jj[t]];
-                }
+            for (int t = 0; t < 4; ++t) acc[t] += sm.M[l * 12 + ii[t]] * sm.PMm[l * 12 + jj[t]];
+        }
 #pragma unroll
-                for (int t = 0; t < 4; ++t)
-                    if (lane + 32 * t < cnt2) sm.G[ii[t] * 12 + jj[t]] += acc[t];
-            }
-            if (lane < nn) {                                   // g += M^T tv
-                double a = 0.0;
-                for (int l = 0; l < dnn; ++l) a += sm.M[l * 12 + lane] * sm.tv[l];
-                sm.g[lane] += a;
-            }
-            __syncwarp();
+        for (int t = 0; t < 4; ++t)
+            if (lane + 32 * t < cnt2) sm.G[ii[t] * 12 + jj[t]] += acc[t];
+    }
+    if (lane < nn) {                                   // g += M^T tv
+        double a = 0.0;
+        for (int l = 0; l < dnn; ++l) a += sm.M[l * 12 + lane] * sm.tv[l];
+        sm.g[lane] += a;
+    }
+    __syncwarp();
 }
 
 // compile-time shapes: every lane owns a 2x2 block of the result (one shared-memory load per multiply-add instead of
@@ -764,11 +821,12 @@ __device__ __forceinline__ void stage_products(WarpSm& sm, int lane) {
             if (j0 + 1 < NN) sm.PMm[(i0 + 1) * 12 + j0 + 1] = a11;
         }
     }
-    if (lane < DN) {                                       // tv = P r + p
-        double a = sm.p[lane];
+    if (lane >= 32 - DN) {                                 // tv = P r + p on the idle lanes
+        const int i = lane - (32 - DN);
+        double a = sm.p[i];
 #pragma unroll
-        for (int l = 0; l < DN; ++l) a += sm.P[lane * 10 + l] * sm.r[l];
-        sm.tv[lane] = a;
+        for (int l = 0; l < DN; ++l) a += sm.P[i * 10 + l] * sm.r[l];
+        sm.tv[i] = a;
     }
     __syncwarp();
     if (lane < CB * (CB + 1) / 2) {                        // upper block triangle of G += M^T (P M)
@@ -808,21 +866,22 @@ __device__ __forceinline__ void stage_products(WarpSm& sm, int lane) {
 // the same products with one entry per thread (block-wide groups).  `blocked` = the warp path would use the register-
 // blocked template for this shape: there only the upper block triangle of G is computed and mirrored, which this
 // reproduces entry for entry (2x2 blocks: (i,j) with i/2 > j/2 takes the value computed for (j,i)).
-__device__ __forceinline__ void stage_products_wide(WarpSm& sm, int rank, int nt, int dnn, int nn, bool blocked) {
-    for (int e = rank; e < dnn * nn; e += nt) {                 // PMm = P M
+template <int NT>
+__device__ __forceinline__ void stage_products_wide(WarpSm& sm, int rank, int dnn, int nn, bool blocked) {
+    for (int e = rank; e < dnn * nn; e += NT) {                 // PMm = P M
         const int i = e / nn, j = e - i * nn;
         double acc = 0.0;
         for (int l = 0; l < dnn; ++l) acc += sm.P[i * 10 + l] * sm.M[l * 12 + j];
         sm.PMm[i * 12 + j] = acc;
     }
-    if (rank >= nt - 16 && rank - (nt - 16) < dnn) {            // tv = P r + p
-        const int i = rank - (nt - 16);
+    if (rank >= NT - 16 && rank - (NT - 16) < dnn) {            // tv = P r + p
+        const int i = rank - (NT - 16);
         double a = sm.p[i];
         for (int l = 0; l < dnn; ++l) a += sm.P[i * 10 + l] * sm.r[l];
         sm.tv[i] = a;
     }
-    gsync(nt);
-    for (int e = rank; e < nn * nn; e += nt) {                  // G += M^T (P M)
+    gsync<NT>();
+    for (int e = rank; e < nn * nn; e += NT) {                  // G += M^T (P M)
         const int i = e / nn, j = e - i * nn;
         const bool mirror = blocked && (i >> 1) > (j >> 1);
         const int ii = mirror ? j : i, jj = mirror ? i : j;
@@ -830,20 +889,15 @@ __device__ __forceinline__ void stage_products_wide(WarpSm& sm, int rank, int nt
         for (int l = 0; l < dnn; ++l) acc += sm.M[l * 12 + ii] * sm.PMm[l * 12 + jj];
         sm.G[i * 12 + j] += acc;
     }
-    if (rank >= nt - 16 && rank - (nt - 16) < nn) {             // g += M^T tv
-        const int c = rank - (nt - 16);
+    if (rank >= NT - 16 && rank - (NT - 16) < nn) {             // g += M^T tv
+        const int c = rank - (NT - 16);
         double a = 0.0;
         for (int l = 0; l < dnn; ++l) a += sm.M[l * 12 + c] * sm.tv[l];
         sm.g[c] += a;
     }
-    gsync(nt);
+    gsync<NT>();
 }
 
-// Backward Riccati sweep + forward substitution of the condensed KKT system
-//   [Hc + delta I  Jg^T] [dw  ]   [-(rd - mu v1 + v2)]
-//   [Jg            0   ] [dlam] = [-g                ]
-// Returns false when some reduced Hessian block is not positive definite (wrong inertia for this delta).
-// The per-stage blocks are streamed through a shared-memory ring with cp.async, several stages ahead of the math.
 // warp prefix / suffix sums (inclusive) used by the s / t passes
 __device__ __forceinline__ double warp_scan_up(double v, int lane) {
 #pragma unroll
@@ -856,10 +910,18 @@ __device__ __forceinline__ double warp_scan_down(double v, int lane) {
     return v;
 }
 
-__device__ __noinline__ bool riccati(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int rank, int nt, double mu, double delta, bool soc) {
+// Backward Riccati sweep + forward substitution of the condensed KKT system
+//   [Hc + delta I  Jg^T] [dw  ]   [-(rd - mu v1 + v2)]
+//   [Jg            0   ] [dlam] = [-g                ]
+// Returns false when some reduced Hessian block is not positive definite (wrong inertia for this delta).
+// The per-stage blocks are streamed through a shared-memory ring with cp.async, several stages ahead of the math;
+// every stage matrix is assembled by table-driven copies out of the staged block (KindTab).
+template <int NT>
+__device__ __noinline__ bool riccati(const Prob& pr, const Ws& ws, WarpSm& sm, const KindTab* tabs, int b, int rank, double mu, double delta, bool soc) {
     const int H = pr.H, N = pr.N;
     // second-order correction: same matrix, residuals replaced by the accumulated c_soc (IPOPT 2.4 / Alg. A-5.7)
-    const int a_gres = soc ? W_GS : W_GRES, a_dy = soc ? W_DY2 : W_DY, a_dlam = soc ? W_DLAM2 : W_DLAM;
+    const int o_gres = soc ? O_GS : O_GRES_C, o_dy = soc ? O_DIR2 : O_DIR, o_dlam = o_dy + 10;
+    double* const rec0 = ws.rec(b, 0);
     const double sf = ws.scal(b)[S_SF];
     bool ok = true;
     // ---- pre-pass (first warp, lanes over stages): direction of s = running sum of its equality residuals;
@@ -868,201 +930,193 @@ __device__ __noinline__ bool riccati(const Prob& pr, const Ws& ws, WarpSm& sm, i
         double carry = 0.0;
         for (int base = 0; base < H; base += 32) {
             const int k = base + rank;
-            double v = k < H ? -ws.at(b, a_gres, k)[k < N ? IS : QS] : 0.0;
+            double* rec = rec0 + k * WS_PER_STAGE;
+            double v = k < H ? -rec[o_gres + (k < N ? IS : QS)] : 0.0;
             v = warp_scan_up(v, rank) + carry;
-            if (k < H) { ws.at(b, a_dy, k)[k < N ? IS : QS] = v; ws.at(b, W_AUX, k)[0] = v; }
+            if (k < H) { rec[o_dy + (k < N ? IS : QS)] = v; rec[O_AUX] = v; }
             carry = __shfl_sync(FULL, v, 31);
         }
         carry = 0.0;
         for (int base = ((H - 1) / 32) * 32; base >= 0; base -= 32) {
             const int k = base + rank;
-            double v = k < H ? ws.at(b, W_RD, k)[k < N ? IT : QT] : 0.0;
+            double* rec = rec0 + k * WS_PER_STAGE;
+            double v = k < H ? rec[O_RD + (k < N ? IT : QT)] : 0.0;
             v = warp_scan_down(v, rank) + carry;
             if (k < H) {
-                ws.at(b, a_dlam, k)[k < N ? IT : QT] = -v;
-                if (k >= 1) ws.at(b, W_AUX, k - 1)[1] = v;
-                if (k == H - 1) ws.at(b, W_AUX, k)[1] = 0.0;
+                rec[o_dlam + (k < N ? IT : QT)] = -v;
+                if (k >= 1) rec[O_AUX + 1 - WS_PER_STAGE] = v;
+                if (k == H - 1) rec[O_AUX + 1] = 0.0;
             }
             carry = __shfl_sync(FULL, v, 0);
         }
     }
-    gsync(nt);
-    for (int j = 1; j < BWD_DEPTH; ++j) stage_fetch_bwd(ws, sm, b, H - j, rank, nt);
+    gsync<NT>();
+    for (int j = 1; j <= BWD_DEPTH; ++j) stage_fetch_bwd(rec0, sm, H - j, rank, NT);
+    cp_async_wait<BWD_DEPTH - 1>();
+    gsync<NT>();
     for (int k = H - 1; k >= 0; --k) {
-        stage_fetch_bwd(ws, sm, b, k - (BWD_DEPTH - 1), rank, nt);
-        const RDims d = rdims(N, k);
-        const int n = d.n, nn = n + 2, nact = d.nxr + 2;
-        const int rcp_nn = 65536 / nn + 1, rcp_n = 65536 / n + 1;
-        for (int e = rank; e < 144; e += nt) sm.G[e] = 0.0;
-        for (int e = rank; e < 120; e += nt) sm.M[e] = 0.0;
-        cp_async_wait<BWD_DEPTH - 1>();
-        gsync(nt);
+        const KindTab& T = tabs[stage_kind(k, N, H)];
+        const int n = T.n, nn = T.nn, nxr = T.nxr;
         const double* sb = sm.ring + (k % BWD_DEPTH) * BWD_SLOT;
-        {   // stage Hessian block over the active variables
-            const int npair = d.st ? 36 : 15;
-            for (int q = rank; q < npair; q += nt) {
-                int ia = (int)((sqrtf(8.0f * q + 1.0f) - 1.0f) * 0.5f);
-                if ((ia + 1) * (ia + 2) / 2 <= q) ++ia;
-                if (ia * (ia + 1) / 2 > q) --ia;
-                const int ib = q - ia * (ia + 1) / 2;
-                const int pa = apos(d, ia), pb = apos(d, ib);
-                const double v = sb[O_HC + q];
-                sm.G[pa * 12 + pb] = v;
-                sm.G[pb * 12 + pa] = v;
+        double* rec = rec0 + k * WS_PER_STAGE;
+        {   // ---- assemble G (stage Hessian over [x^ | p | u] + closed-form parts), M, the linear term g
+            const double* ob = sb + O_OBS;
+            const double cc0 = 2.0 * sf * ob[6], cc1 = 2.0 * sf * ob[7], eyey = sf * ob[5];
+            for (int e = rank; e < T.ng; e += NT) {
+                const int src = T.gsrc[e], fl = T.gflag[e];
+                double v = src >= 0 ? sb[src] : 0.0;
+                if (fl) {
+                    if (fl & GF_EY) v += eyey;
+                    if (fl & GF_P0) v += cc0;
+                    if (fl & GF_M0) v -= cc0;
+                    if (fl & GF_P1) v += cc1;
+                    if (fl & GF_M1) v -= cc1;
+                    if (fl & GF_DELTA) v += delta;
+                }
+                sm.G[T.gdst[e]] = v;
+            }
+            for (int e = rank; e < T.nm; e += NT) {
+                const int src = T.msrc[e];
+                sm.M[T.mdst[e]] = src >= 0 ? sb[O_AB + src] : (src == -2 ? 1.0 : 0.0);
             }
             // linear term of active variable a on lane a of the LAST warp of the group
-            const int a = rank - (nt - 32);
-            if (a >= 0 && a < nact) {
-                const int yi = yidx(d, a);   // (a >= nxr: the controls, which c_act_* lists last)
+            const int a = rank - (NT - 32);
+            if (a >= 0 && a < nxr + 2) {
+                const int yi = yidx(T.st != 0, a);
                 double f = sb[O_RD + yi] - mu * sb[O_V1 + yi] + sb[O_V2 + yi];
                 if (soc) {   // + Jc^T sigma (c_soc - (c - s))
-                    const double *jc = ws.at(b, W_JC, k), *cs = ws.at(b, W_CS, k), *cr = ws.at(b, W_CRES, k);
-                    const double *sl = ws.at(b, W_S, k), *z = ws.at(b, W_Z, k);
-                    for (int j = 0; j < (d.st ? NI_ST : NI_PM); ++j)
+                    const double *jc = rec + O_JC, *cs = rec + O_CS, *cr = rec + O_CRES;
+                    const double *sl = rec + O_S, *z = rec + O_Z;
+                    for (int j = 0; j < (T.st ? NI_ST : NI_PM); ++j)
                         f += jc[j * 8 + a] * (z[j] / sl[j]) * (cs[j] - (cr[j] - sl[j]));
                 }
-                if (yi == (d.st ? IEY : QEY)) f += sf * sb[O_OBS + 4] * sb[O_AUX];          // obstacle cross term (s, ey) x ds
-                if (k < H - 1) f += sb[O_AB + (k + 1 < N ? IT : QT) * 8 + a] * sb[O_AUX + 1];   // d t_{k+1} / d a x cost-to-go of t
-                sm.g[apos(d, a)] = f;
-            }
-            if (a >= d.nxr + 2 && a < d.nxr + 2 + d.np) sm.g[a - 2] = 0.0;   // lifted variables carry no linear term
-            if (k < H - 1) scatter_transition(sm, sb + O_AB, rank, nt, d, rdims(N, k + 1));
+                if (yi == (T.st ? IEY : QEY)) f += sf * ob[4] * sb[O_AUX];            // obstacle cross term (s, ey) x ds
+                if (T.has_next) f += sb[O_AB + T.trow * 8 + a] * sb[O_AUX + 1];       // d t_{k+1} / d a x cost-to-go of t
+                sm.g[a < nxr ? a : n + (a - nxr)] = f;
+            } else if (a >= nxr + 2 && a < n + 2) sm.g[a - 2] = 0.0;                  // lifted variables: no linear term
         }
-        gsync(nt);
-        {   // closed-form Hessian parts: obstacle term (rank 0), control-continuity terms (ranks 1, 2), delta_w
-            const double* ob = sb + O_OBS;
-            if (rank == 0) {
-                const int eyp = d.st ? 4 : 1;
-                sm.G[eyp * 12 + eyp] += sf * ob[5];
-            } else if (rank <= d.np) {
-                const int j = rank - 1;
-                const double cc = 2.0 * sf * ob[6 + j];
-                sm.G[(n + j) * 12 + n + j] += cc;
-                sm.G[(d.nxr + j) * 12 + d.nxr + j] += cc;
-                sm.G[(n + j) * 12 + d.nxr + j] -= cc;
-                sm.G[(d.nxr + j) * 12 + n + j] -= cc;
-            }
-            if (delta != 0.0) {
-                gsync(nt);
-                if (rank < d.nxr) sm.G[rank * 12 + rank] += delta;
-                if (rank >= 30 && rank < 32) sm.G[(n + rank - 30) * 12 + n + rank - 30] += delta;
-            }
-        }
-        gsync(nt);
-        if (k < H - 1) {
-            const RDims dn = rdims(N, k + 1);
+        gsync<NT>();
+        if (T.has_next) {
             // G += M^T P M, g += M^T (P r + p): register-blocked for the stage shapes of the shipped controllers
-            const bool blocked = (dn.n == 7 && (nn == 9 || nn == 8)) || (dn.n == 5 && (nn == 7 || nn == 9));
-            if (nt != 32) stage_products_wide(sm, rank, nt, dn.n, nn, blocked);
-            else if (dn.n == 7 && nn == 9) stage_products<7, 9>(sm, rank);
-            else if (dn.n == 5 && nn == 7) stage_products<5, 7>(sm, rank);
-            else if (dn.n == 5 && nn == 9) stage_products<5, 9>(sm, rank);
-            else if (dn.n == 7 && nn == 8) stage_products<7, 8>(sm, rank);
-            else stage_products_generic(sm, rank, dn.n, nn, rcp_nn);
+            const int dnn = T.dnn;
+            const bool blocked = (dnn == 7 && (nn == 9 || nn == 8)) || (dnn == 5 && (nn == 7 || nn == 9));
+            if (NT != 32) stage_products_wide<NT>(sm, rank, dnn, nn, blocked);
+            else if (dnn == 7 && nn == 9) stage_products<7, 9>(sm, rank);
+            else if (dnn == 5 && nn == 7) stage_products<5, 7>(sm, rank);
+            else if (dnn == 5 && nn == 9) stage_products<5, 9>(sm, rank);
+            else if (dnn == 7 && nn == 8) stage_products<7, 8>(sm, rank);
+            else stage_products_generic(sm, rank, dnn, nn);
         }
-        // reduced Hessian of the two controls
+        // ---- reduced Hessian of the two controls, feedback gains, cost-to-go of this stage (one phase: every thread
+        // derives the gain columns it needs from G itself)
         const double ra = sm.G[n * 12 + n], rb = 0.5 * (sm.G[n * 12 + n + 1] + sm.G[(n + 1) * 12 + n]),
                      rdd = sm.G[(n + 1) * 12 + n + 1];
         const double det = ra * rdd - rb * rb;
         if (!(ra > 0.0) || !(det > 0.0) || !isfinite(det)) { ok = false; break; }
         const double idet = 1.0 / det;
         const double i00 = rdd * idet, i01 = -rb * idet, i11 = ra * idet;
-        double* km = ws.at(b, W_KM, k);
+        const double gu0 = sm.g[n], gu1 = sm.g[n + 1];
+        const double f0 = -(i00 * gu0 + i01 * gu1), f1 = -(i01 * gu0 + i11 * gu1);   // feed-forward
+        double* km = rec + O_KM;
         if (rank < n) {
             const double g0 = sm.G[n * 12 + rank], g1 = sm.G[(n + 1) * 12 + rank];
-            const double k0 = -(i00 * g0 + i01 * g1), k1 = -(i01 * g0 + i11 * g1);
-            sm.K[rank] = k0; sm.K[12 + rank] = k1;
-            km[rank] = k0; km[10 + rank] = k1;
+            km[rank] = -(i00 * g0 + i01 * g1); km[10 + rank] = -(i01 * g0 + i11 * g1);
         }
-        if (rank == 31) {
-            const double g0 = sm.g[n], g1 = sm.g[n + 1];
-            const double f0 = -(i00 * g0 + i01 * g1), f1 = -(i01 * g0 + i11 * g1);
-            sm.K[10] = f0; sm.K[22] = f1;
-            km[20] = f0; km[21] = f1;
-        }
-        // the equality residual of THIS stage's state is the offset of the transition into it (used at stage k-1)
-        if (rank >= 12 && rank < 24) {
-            const int q = rank - 12;
-            sm.r[q] = q < d.nxr ? -(soc ? ws.at(b, a_gres, k)[yidx(d, q)] : sb[O_GRES + yidx(d, q)]) : 0.0;
-        }
-        gsync(nt);
-        double* pm = ws.at(b, W_PM, k);
-        double* pv = ws.at(b, W_PV, k);
-        for (int e = rank; e < n * n; e += nt) {               // P = Gxx + Gxu K   (symmetrised)
+        if (rank == 31) { km[20] = f0; km[21] = f1; }
+        double* pm = rec + O_PM;
+        double* pv = rec + O_PV;
+        const int rcp_n = 65536 / n + 1;
+        for (int e = rank; e < n * n; e += NT) {               // P = Gxx + Gxu K   (symmetrised)
             const int i = (e * rcp_n) >> 16, j = e - i * n;
-            const double a = sm.G[i * 12 + j] + sm.G[i * 12 + n] * sm.K[j] + sm.G[i * 12 + n + 1] * sm.K[12 + j];
-            const double c = sm.G[j * 12 + i] + sm.G[j * 12 + n] * sm.K[i] + sm.G[j * 12 + n + 1] * sm.K[12 + i];
+            const double gi0 = sm.G[n * 12 + i], gi1 = sm.G[(n + 1) * 12 + i], gj0 = sm.G[n * 12 + j], gj1 = sm.G[(n + 1) * 12 + j];
+            const double ki0 = -(i00 * gi0 + i01 * gi1), ki1 = -(i01 * gi0 + i11 * gi1);
+            const double kj0 = -(i00 * gj0 + i01 * gj1), kj1 = -(i01 * gj0 + i11 * gj1);
+            const double a = sm.G[i * 12 + j] + sm.G[i * 12 + n] * kj0 + sm.G[i * 12 + n + 1] * kj1;
+            const double c = sm.G[j * 12 + i] + sm.G[j * 12 + n] * ki0 + sm.G[j * 12 + n + 1] * ki1;
             const double v = 0.5 * (a + c);
             sm.P[i * 10 + j] = v;
             pm[i * 10 + j] = v;
         }
         {
-            const int q = rank - (nt - 16);                    // last half-warp of the group
+            const int q = rank - (NT - 16);                    // last half-warp of the group
             if (q >= 0 && q < n) {
-                const double v = sm.g[q] + sm.G[q * 12 + n] * sm.K[10] + sm.G[q * 12 + n + 1] * sm.K[22];
+                const double v = sm.g[q] + sm.G[q * 12 + n] * f0 + sm.G[q * 12 + n + 1] * f1;
                 sm.p[q] = v;
                 pv[q] = v;
             }
+            // the equality residual of THIS stage's state is the offset of the transition into it (used at stage k-1)
+            const int q2 = rank - (NT - 32);
+            if (q2 >= 0 && q2 < 12) sm.r[q2] = q2 < nxr ? -(soc ? rec[o_gres + yidx(T.st != 0, q2)] : sb[O_GRES + yidx(T.st != 0, q2)]) : 0.0;
         }
-        gsync(nt);
+        // the slot of stage k is free after the barrier: queue stage k - BWD_DEPTH; stage k - 1 must have landed
+        cp_async_wait<BWD_DEPTH - 2>();
+        gsync<NT>();
+        stage_fetch_bwd(rec0, sm, k - BWD_DEPTH, rank, NT);
     }
     cp_async_wait<0>();
-    gsync(nt);
+    gsync<NT>();
     if (!ok) return false;
-    // ---- forward substitution (stage blocks AB | GRES KM PV PM streamed two stages ahead)
-    for (int j = 0; j < FWD_DEPTH - 1; ++j) stage_fetch_fwd(ws, sm, b, j, H, rank, nt);
-    stage_fetch_fwd(ws, sm, b, FWD_DEPTH - 1, H, rank, nt);
-    cp_async_wait<FWD_DEPTH - 1>();
-    gsync(nt);
-    if (rank < 12) {
-        const RDims d0 = rdims(N, 0);
-        sm.x[rank] = rank < d0.nxr ? -(soc ? ws.at(b, a_gres, 0)[yidx(d0, rank)] : sm.ring[F_GRES + yidx(d0, rank)]) : 0.0;
+    // ---- forward substitution (stage blocks AB | GRES KM PV PM streamed ahead); x ping-pongs between two buffers
+    for (int j = 0; j < FWD_DEPTH; ++j) stage_fetch_fwd(rec0, sm, j, H, rank, NT);
+    cp_async_wait<FWD_DEPTH - 2>();          // stages 0 and 1
+    gsync<NT>();
+    double* xc = sm.x;
+    double* xn = sm.tv;
+    {
+        const KindTab& T0 = tabs[stage_kind(0, N, H)];
+        if (rank < 12) xc[rank] = rank < T0.nxr ? -(soc ? rec0[o_gres + yidx(T0.st != 0, rank)] : sm.ring[F_GRES + yidx(T0.st != 0, rank)]) : 0.0;
     }
-    gsync(nt);
+    gsync<NT>();
     for (int k = 0; k < H; ++k) {
-        const RDims d = rdims(N, k);
-        const int n = d.n;
+        const KindTab& T = tabs[stage_kind(k, N, H)];
+        const int n = T.n, nxr = T.nxr;
         const double* fb = sm.ring + (k % FWD_DEPTH) * FWD_SLOT;
-        if (rank < 2) {
-            const double* km = fb + F_KM;
-            double a = km[20 + rank];
-            for (int l = 0; l < n; ++l) a += km[rank * 10 + l] * sm.x[l];
-            sm.x[n + rank] = a;
-        }
-        if (k < H - 1) for (int e = rank; e < 120; e += nt) sm.M[e] = 0.0;
-        gsync(nt);
-        double* dy = ws.at(b, a_dy, k);
+        double* rec = rec0 + k * WS_PER_STAGE;
+        // controls u = K x + kff: every thread that needs them computes them (two short dot products, no barrier)
+        double u0, u1;
         {
-            const int q = rank - (nt - 16);                    // multiplier direction on the last half-warp
-            if (q >= 0 && q < d.nxr) {
+            const double* km = fb + F_KM;
+            u0 = km[20]; u1 = km[21];
+            for (int l = 0; l < n; ++l) { const double xl = xc[l]; u0 += km[l] * xl; u1 += km[10 + l] * xl; }
+        }
+        double* dy = rec + o_dy;
+        const bool st = T.st != 0;
+        if (rank < nxr) dy[yidx(st, rank)] = xc[rank];
+        if (rank == 30) dy[st ? 8 : 5] = u0;
+        if (rank == 31) dy[st ? 9 : 6] = u1;
+        {
+            const int q = rank - (NT - 16);                    // multiplier direction on the last half-warp
+            if (q >= 0 && q < nxr) {
                 const double* pm = fb + F_PM;
                 double a = fb[F_PV + q];
-                for (int l = 0; l < n; ++l) a += pm[q * 10 + l] * sm.x[l];
-                ws.at(b, a_dlam, k)[yidx(d, q)] = -a;
+                for (int l = 0; l < n; ++l) a += pm[q * 10 + l] * xc[l];
+                rec[o_dlam + yidx(st, q)] = -a;
             }
         }
-        if (rank < d.nxr) dy[yidx(d, rank)] = sm.x[rank];
-        if (rank < 2) dy[d.nuo + rank] = sm.x[n + rank];
-        if (k < H - 1) {
-            const RDims dn = rdims(N, k + 1);
-            scatter_transition(sm, fb + F_AB, rank, nt, d, dn);
-            cp_async_wait<FWD_DEPTH - 2>();     // stage k+1's block (its GRES is the offset of this transition)
-            gsync(nt);
+        if (T.has_next) {
+            const bool nst = T.nst != 0;
+            const int dnxr = T.dnxr, dnn = T.dnn;
             const double* fn = sm.ring + ((k + 1) % FWD_DEPTH) * FWD_SLOT;
-            double a = 0.0;
-            if (rank < dn.n) {
-                a = rank < dn.nxr ? -(soc ? ws.at(b, a_gres, k + 1)[yidx(dn, rank)] : fn[F_GRES + yidx(dn, rank)]) : 0.0;
-                for (int l = 0; l < n + 2; ++l) a += sm.M[rank * 12 + l] * sm.x[l];
+            if (rank < dnn) {
+                double a;
+                if (rank < dnxr || (rank == dnxr + 1 && st && !nst)) {
+                    // next reduced state component (or, at the switch, the lifted T): row of [A B] times (x^, u)
+                    const int row = rank < dnxr ? yidx(nst, rank) : 5;
+                    a = rank < dnxr ? -(soc ? rec[WS_PER_STAGE + o_gres + row] : fn[F_GRES + row]) : 0.0;
+                    const double* abr = fb + F_AB + row * 8;
+                    for (int l = 0; l < nxr; ++l) a += abr[l] * xc[l];
+                    a += abr[nxr] * u0 + abr[nxr + 1] * u1;
+                } else a = rank == dnxr ? u0 : u1;             // lifted copies of the controls
+                xn[rank] = a;
             }
-            gsync(nt);
-            if (rank < dn.n) sm.x[rank] = a;
-            // slot of stage k is free now: stream stage k + FWD_DEPTH into it
-            stage_fetch_fwd(ws, sm, b, k + FWD_DEPTH, H, rank, nt);
-            gsync(nt);
         }
+        cp_async_wait<FWD_DEPTH - 3>();      // stage k + 2 has landed (queued two stages ago)
+        gsync<NT>();
+        stage_fetch_fwd(rec0, sm, k + FWD_DEPTH, H, rank, NT);   // into the slot of stage k, free after the barrier
+        double* t = xc; xc = xn; xn = t;
     }
     cp_async_wait<0>();
-    gsync(nt);
+    gsync<NT>();
     // ---- post-pass (first warp, lanes over stages): direction of t = running sum of its linearised increments;
     // multiplier direction of s = running sum (from the end) of its stationarity row
     if (rank < 32) {
@@ -1071,16 +1125,17 @@ __device__ __noinline__ bool riccati(const Prob& pr, const Ws& ws, WarpSm& sm, i
             const int k = base + rank;
             double v = 0.0;
             if (k < H) {
-                v = -ws.at(b, a_gres, k)[k < N ? IT : QT];
+                const double* rec = rec0 + k * WS_PER_STAGE;
+                v = -rec[o_gres + (k < N ? IT : QT)];
                 if (k >= 1) {
-                    const RDims dp = rdims(N, k - 1);
-                    const double* ab = ws.at(b, W_AB, k - 1) + (k < N ? IT : QT) * 8;
-                    const double* dyp = ws.at(b, a_dy, k - 1);
-                    for (int a = 0; a < dp.nxr + 2; ++a) v += ab[a] * dyp[yidx(dp, a)];
+                    const bool pst = k - 1 < N;
+                    const double* ab = rec - WS_PER_STAGE + O_AB + (k < N ? IT : QT) * 8;
+                    const double* dyp = rec - WS_PER_STAGE + o_dy;
+                    for (int a = 0; a < (pst ? 8 : 5); ++a) v += ab[a] * dyp[yidx(pst, a)];
                 }
             }
             v = warp_scan_up(v, rank) + carry;
-            if (k < H) ws.at(b, a_dy, k)[k < N ? IT : QT] = v;
+            if (k < H) rec0[k * WS_PER_STAGE + o_dy + (k < N ? IT : QT)] = v;
             carry = __shfl_sync(FULL, v, 31);
         }
         carry = 0.0;
@@ -1088,44 +1143,45 @@ __device__ __noinline__ bool riccati(const Prob& pr, const Ws& ws, WarpSm& sm, i
             const int k = base + rank;
             double v = 0.0;
             if (k < H) {
-                const double* ob = ws.at(b, W_OBS, k);
-                const double* dyk = ws.at(b, a_dy, k);
-                v = ws.at(b, W_RD, k)[k < N ? IS : QS] + sf * (ob[3] * dyk[k < N ? IS : QS] + ob[4] * dyk[k < N ? IEY : QEY]);
+                const double* rec = rec0 + k * WS_PER_STAGE;
+                const double* ob = rec + O_OBS;
+                const double* dyk = rec + o_dy;
+                v = rec[O_RD + (k < N ? IS : QS)] + sf * (ob[3] * dyk[k < N ? IS : QS] + ob[4] * dyk[k < N ? IEY : QEY]);
             }
             v = warp_scan_down(v, rank) + carry;
-            if (k < H) ws.at(b, a_dlam, k)[k < N ? IS : QS] = -v;
+            if (k < H) rec0[k * WS_PER_STAGE + o_dlam + (k < N ? IS : QS)] = -v;
             carry = __shfl_sync(FULL, v, 0);
         }
     }
-    gsync(nt);
+    gsync<NT>();
     return true;
 }
 
 // ---- helper threads of a block-wide group: warp 0 runs the (scalar) interior-point logic of its instance and calls
 // the others in for the factorisations.  Commands go through shared memory, hand-over by the named barrier.
+constexpr int WIDE_NT = 128;
 enum GroupOp { OP_EXIT = 0, OP_RICCATI = 1 };
 struct GroupCmd { int op, soc; double mu, delta; };
-struct Group { int rank, nt; GroupCmd* cmd; };   // cmd == nullptr for a warp group
+struct Group { int rank, nt; GroupCmd* cmd; const KindTab* tabs; };   // cmd == nullptr for a warp group
 
 __device__ __forceinline__ bool riccati_call(const Prob& pr, const Ws& ws, WarpSm& sm, int b, const Group& g, double mu, double delta, bool soc) {
-    if (g.nt != 32) {
-        if (g.rank == 0) { g.cmd->op = OP_RICCATI; g.cmd->soc = soc; g.cmd->mu = mu; g.cmd->delta = delta; }
-        gsync(g.nt);   // releases the helpers (group_helpers)
-    }
-    return riccati(pr, ws, sm, b, g.rank, g.nt, mu, delta, soc);
+    if (g.nt == 32) return riccati<32>(pr, ws, sm, g.tabs, b, g.rank, mu, delta, soc);
+    if (g.rank == 0) { g.cmd->op = OP_RICCATI; g.cmd->soc = soc; g.cmd->mu = mu; g.cmd->delta = delta; }
+    gsync<WIDE_NT>();   // releases the helpers (group_helpers)
+    return riccati<WIDE_NT>(pr, ws, sm, g.tabs, b, g.rank, mu, delta, soc);
 }
 __device__ __forceinline__ void group_helpers(const Prob& pr, const Ws& ws, WarpSm& sm, int b, const Group& g) {
     for (;;) {
-        gsync(g.nt);
+        gsync<WIDE_NT>();
         const GroupCmd c = *g.cmd;
         if (c.op == OP_EXIT) return;
-        riccati(pr, ws, sm, b, g.rank, g.nt, c.mu, c.delta, c.soc != 0);
+        riccati<WIDE_NT>(pr, ws, sm, g.tabs, b, g.rank, c.mu, c.delta, c.soc != 0);
     }
 }
 __device__ __forceinline__ void group_release(const Group& g) {   // called by warp 0 when its instance's step is finished
     if (g.nt == 32) return;
     if (g.rank == 0) g.cmd->op = OP_EXIT;
-    gsync(g.nt);
+    gsync<WIDE_NT>();
 }
 
 // slack / multiplier directions of a computed primal direction, fraction-to-the-boundary step sizes and the
@@ -1245,28 +1301,10 @@ __device__ __noinline__ void repair_rollout(const Prob& pr, const Ws& ws, int b,
             const int si = k < N ? IS : QS, eyi = k < N ? IEY : QEY;
             for (int o = 0; o < pr.n_obs; ++o) {
                 const double R = ob[3 * o + 2] + 0.1 + 0.5, a = y[si] - ob[3 * o], e = y[eyi] - ob[3 * o + 1];
-                if (a * a + e * e < R * R) y[eyi] = ob[3 * o + 1] + (e > 0.0 ? 1.0 : -1.0) * sqrt(R * R - a * a);
+                if (a * a + e * e < R * R) y[eyi] = ob[3 * o + 1] + (e > 1e-9 ? 1.0 : -1.0) * sqrt(R * R - a * a);   // |e| <= 1e-9: dead centre
             }
         }
     }
-}
-
-// a restored trajectory is only useful if it stays inside the (slightly widened) state bounds: rolling out controls
-// that are still far from sensible (cold starts) spins the car or leaves the track
-__device__ __noinline__ bool rollout_sane(const Prob& pr, const Ws& ws, int b) {
-    const Cfg& c = pr.c;
-    for (int k = 0; k < pr.H; ++k) {
-        const double* y = ws.at(b, W_Y, k);
-        if (k < pr.N) {
-            for (int i = 0; i < 8; ++i) if (!isfinite(y[i])) return false;
-            if (y[IUX] < c.Ux_min || y[IDELTA] < c.delta_min - 0.05 || y[IDELTA] > c.delta_max + 0.05) return false;
-            if (y[IEY] < c.ey_min - 1.0 || y[IEY] > c.ey_max + 1.0 || fabs(y[IEPSI]) > 1.0) return false;
-        } else {
-            for (int i = 0; i < 5; ++i) if (!isfinite(y[i])) return false;
-            if (y[QV] < c.V_min || y[QEY] < c.ey_min_pm - 1.0 || y[QEY] > c.ey_max_pm + 1.0 || fabs(y[QEPSI]) > 1.0) return false;
-        }
-    }
-    return true;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1319,29 +1357,6 @@ __device__ void step_part_a(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int
         mu = fmax(mu_floor, fmin(IpmConst::kappa_mu * mu, pow(mu, IpmConst::theta_mu)));
         nfilt = 0;
     }
-    // stall escape (stands in for IPOPT's watchdog): several consecutive heavily shortened steps mean the Newton
-    // model of this barrier problem is poor where the iterate sits; the barrier problem need not be solved
-    // accurately for path following, so move on to the next rung
-    int n_short = (int)sc[S_SHORT];
-    if (n_short >= pr.stall_iters && mu > mu_floor * (1 + 1e-12)) {
-        mu = fmax(mu_floor, fmin(IpmConst::kappa_mu * mu, pow(mu, IpmConst::theta_mu)));
-        nfilt = 0; n_short = 0;
-    }
-    // feasibility restoration substitute: a run of heavily shortened steps at an infeasible iterate means the
-    // linearisation is poor there (IPOPT would end up in its restoration phase); project the iterate onto the
-    // dynamics manifold by rolling the models out from x0 under the CURRENT controls and restart the barrier
-    // problem from that point (same mu, cleared filter)
-    if (pr.restore_iters > 0 && n_short >= pr.restore_iters && (int)sc[S_NREST] < 3 && m.theta > 1e-6) {
-        if (lane == 0) { sc[S_PHASE] = PH_RESTORE; sc[S_MU_NEW] = mu; }
-        return;
-    }
-    // all restorations used and the steps are still being cut at an infeasible iterate: give the instance up (IPOPT ends
-    // such runs with "restoration failed"); it would otherwise crawl to max_iter and hold the whole batch's tail
-    if (pr.restore_iters > 0 && (int)sc[S_NREST] >= 3 && n_short >= pr.giveup_iters && m.theta > 1e-6 &&
-        !(mu > mu_floor * (1 + 1e-12))) {
-        finalize(pr, ws, b, lane, VC_LINESEARCH_FAIL, obj, err0);
-        return;
-    }
     const double tau = fmax(IpmConst::tau_min, 1.0 - mu);
     const double theta = m.theta, phi = sf * m.f - mu * m.lns;
     double theta0 = sc[S_THETA0];
@@ -1364,7 +1379,7 @@ __device__ void step_part_a(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int
     if (lane == 0) {
         sc[S_PHASE] = failed ? PH_FAILED : PH_SEARCH;
         sc[S_MU_NEW] = mu; sc[S_THETA] = theta; sc[S_PHI] = phi; sc[S_THETA0_NEW] = theta0; sc[S_NFILT_NEW] = nfilt;
-        sc[S_TRIAL] = trial; sc[S_ACC_NEW] = acc; sc[S_NSHORT_NEW] = n_short; sc[S_OBJ_NEW] = obj; sc[S_ERR_NEW] = err0;
+        sc[S_TRIAL] = trial; sc[S_ACC_NEW] = acc; sc[S_OBJ_NEW] = obj; sc[S_ERR_NEW] = err0;
         if (!failed) { sc[S_AP] = a_p; sc[S_AD] = a_d; sc[S_DPHI] = dphi; }
     }
     (void)theta_min; (void)theta_max; (void)iters;
@@ -1389,23 +1404,8 @@ __device__ void step_part_b(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int
     }
     const double mu = sc[S_MU_NEW], sf = sc[S_SF];
     const int iters = (int)sc[S_ITERS];
-    if (phase == PH_RESTORE) {
-        __syncwarp();
-        if (lane == 0) {
-            repair_rollout(pr, ws, b, false);
-            if (pr.restore_check && !rollout_sane(pr, ws, b)) repair_rollout(pr, ws, b, true);   // neutral controls instead
-            sc[S_NREST] += 1.0; sc[S_MODE] = MODE_REINIT; sc[S_SHORT] = 0; sc[S_ITERS] = iters + 1; sc[S_MU] = mu;
-            sc[S_DAMP_TRIAL] = 0.0; sc[S_NDAMP] = 0.0;
-        }
-        for (int k = lane; k < H; k += 32) {
-            double *lam = ws.at(b, W_LAM, k), *s = ws.at(b, W_S, k), *z = ws.at(b, W_Z, k);
-            for (int i = 0; i < 8; ++i) lam[i] = 0.0;
-            for (int j = 0; j < 10; ++j) { s[j] = 1.0; z[j] = 0.0; }
-        }
-        return;
-    }
     const double obj = sc[S_OBJ_NEW], err0 = sc[S_ERR_NEW];
-    const int acc = (int)sc[S_ACC_NEW], n_short = (int)sc[S_NSHORT_NEW];
+    const int acc = (int)sc[S_ACC_NEW];
     int nfilt = (int)sc[S_NFILT_NEW];
     const double theta = sc[S_THETA], phi = sc[S_PHI], theta0 = sc[S_THETA0_NEW];
     const double tau = fmax(IpmConst::tau_min, 1.0 - mu);
@@ -1420,8 +1420,9 @@ __device__ void step_part_b(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int
     double* filt_t = sc + S_FILT;
     double* filt_p = sc + S_FILP;
     bool use_soc = false;
-    // acceptance of a trial point by the filter (IPOPT Alg. A, steps A-5.3/5.4); all lanes hold the same values
-    auto acceptable = [&](double a_test, double tht, double pht, double dphi, bool& augment) -> bool {
+    // acceptance of a trial point by the filter (IPOPT Alg. A, steps A-5.3/5.4) relative to a reference point (the
+    // current iterate, or the stored one while the watchdog runs); all lanes hold the same values
+    auto acceptable_ref = [&](double a_test, double tht, double pht, double dphi, bool& augment, double theta, double phi) -> bool {
         augment = false;
         if (tht > theta_max) return false;
         for (int i = 0; i < nfilt; ++i)
@@ -1437,12 +1438,69 @@ __device__ void step_part_b(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int
         // steps at the rounding floor: both measures unchanged
         return fabs(pht - phi) <= 1e-13 * fmax(1.0, fabs(phi)) && tht <= theta + 1e-13;
     };
+    auto acceptable = [&](double a_test, double tht, double pht, double dphi, bool& augment) -> bool {
+        return acceptable_ref(a_test, tht, pht, dphi, augment, theta, phi);
+    };
+    // ---- IPOPT's watchdog (IpBacktrackingLineSearch StartWatchDog / StopWatchDog): after `watchdog_trigger` consecutive
+    // shortened steps the full step is taken for up to `watchdog_trials` iterations without asking the filter, the
+    // acceptance test being made against the stored reference point; if no acceptable point turns up, the stored iterate
+    // is restored and the regular backtracking follows (first trial point skipped)
+    bool in_wd = sc[S_WD_IN] != 0.0;
+    const bool skip_first = sc[S_SKIP_FIRST] != 0.0;
+    int wd_short = (int)sc[S_WD_SHORT];
+    int n_steps = 0;
+    bool forced = false;
+    if (!failed && !in_wd && pr.watchdog_trigger > 0 && wd_short >= pr.watchdog_trigger && !skip_first && sc[S_DAMP_TRIAL] == 0.0) {
+        in_wd = true;
+        for (int e = lane; e < H * 38; e += 32) {           // store the reference iterate
+            const int k = e / 38, i = e - k * 38;
+            double* r = ws.rec(b, k);
+            r[O_BAK + i] = r[O_IT + i];
+        }
+        if (lane == 0) {
+            sc[S_WD_IN] = 1.0; sc[S_WD_TRIAL] = 0.0; sc[S_WD_THETA] = theta; sc[S_WD_PHI] = phi; sc[S_WD_DPHI] = sc[S_DPHI];
+            sc[S_WD_ATEST] = sc[S_AP];
+        }
+        __syncwarp();
+    }
+    if (!failed && in_wd) {
+        const double a_p = sc[S_AP];
+        double ft, tht, lnt;
+        bool okv;
+        if (cache) { okv = cache[0].ok != 0.0; ft = cache[0].f; tht = cache[0].theta; lnt = cache[0].lns; }
+        else okv = trial_point(pr, ws, b, lane, a_p, false, true, ft, tht, lnt);
+        bool augment = false;
+        const double th_ref = sc[S_WD_THETA], ph_ref = sc[S_WD_PHI];
+        const bool acc_wd = okv && acceptable_ref(sc[S_WD_ATEST], tht, sf * ft - mu * lnt, sc[S_WD_DPHI], augment, th_ref, ph_ref);
+        const int wd_trial = (int)sc[S_WD_TRIAL] + 1;
+        __syncwarp();
+        if (acc_wd) {
+            if (augment && nfilt < FILT_MAX) {
+                if (lane == 0) { filt_t[nfilt] = (1 - IpmConst::gamma_theta) * th_ref; filt_p[nfilt] = ph_ref - IpmConst::gamma_phi * th_ref; }
+                ++nfilt;
+            }
+            if (lane == 0) sc[S_WD_IN] = 0.0;
+            accepted = true; alpha = a_p; dbg_ap = a_p;
+        } else if (!okv || wd_trial > pr.watchdog_trials) {
+            for (int e = lane; e < H * 38; e += 32) {       // back to the stored iterate; the next pass backtracks from it
+                const int k = e / 38, i = e - k * 38;
+                double* r = ws.rec(b, k);
+                r[O_IT + i] = r[O_BAK + i];
+            }
+            if (lane == 0) { sc[S_WD_IN] = 0.0; sc[S_WD_SHORT] = 0.0; sc[S_SKIP_FIRST] = 1.0; sc[S_MU] = mu; sc[S_NFILT] = nfilt; }
+            return;
+        } else {
+            if (lane == 0) sc[S_WD_TRIAL] = wd_trial;
+            accepted = true; forced = true; alpha = a_p; dbg_ap = a_p;   // full step taken on trust
+        }
+    }
     while (!accepted && !failed) {   // one direction per pass (computed by k_step_a)
         const double a_p = sc[S_AP], dphi = sc[S_DPHI];
         dbg_ap = a_p; dbg_dphi = dphi;
         // ---- backtracking filter line search, lanes over stages
-        alpha = a_p;
-        for (int bt = 0; bt < 12 && !accepted; ++bt, alpha *= 0.5) {
+        alpha = skip_first ? 0.5 * a_p : a_p;
+        for (int bt = skip_first ? 1 : 0; bt < 12 && !accepted; ++bt, alpha *= 0.5) {
+            n_steps = bt;
             double ft, tht, lnt;
             bool okv;
             if (cache) { okv = cache[bt].ok != 0.0; ft = cache[bt].f; tht = cache[bt].theta; lnt = cache[bt].lns; }
@@ -1455,7 +1513,7 @@ __device__ void step_part_b(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int
             // not reduced -> re-solve with c_soc = alpha c(x) + c(x + alpha d), at most 4 times
             if (!accepted && bt == 0 && okv && tht >= theta && pr.max_soc > 0) {
                 soc_residual(pr, ws, b, lane, alpha, false, true);
-                double theta_soc_old = theta;
+                double theta_soc_old = tht;   // IPOPT compares every correction with the previous TRIAL point's violation
                 for (int ps = 0; ps < pr.max_soc; ++ps) {
                     if (!riccati_call(pr, ws, sm, b, g, mu, trial, true)) break;
                     double a_p2, a_d2, dphi2, ft2, tht2, lnt2;
@@ -1463,7 +1521,7 @@ __device__ void step_part_b(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int
                     const bool ok2 = trial_point(pr, ws, b, lane, a_p2, true, true, ft2, tht2, lnt2);
                     if (ps == 0) { dbg_tht2 = ok2 ? tht2 : -1.0; dbg_ap2 = a_p2; }
                     if (ok2 && acceptable(alpha, tht2, sf * ft2 - mu * lnt2, dphi, augment)) {
-                        accepted = true; use_soc = true; alpha = a_p2; a_d = a_d2;
+                        accepted = true; use_soc = true; alpha = a_p2; a_d = a_d2; n_steps = 0;
                         break;
                     }
                     if (!ok2 || tht2 > 0.99 * theta_soc_old) break;
@@ -1511,8 +1569,10 @@ __device__ void step_part_b(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int
     // ---- accept: the primal-dual update itself is streaming work (38 doubles per stage read twice, written once) and
     // runs in k_update at full occupancy; here only its parameters are handed over
     if (lane == 0) { sc[S_UPD_DIR] = use_soc ? 2.0 : 1.0; sc[S_UPD_ALPHA] = alpha; sc[S_UPD_AD] = a_d; }
+    (void)forced;
     if (lane == 0) {
-        sc[S_SHORT] = (alpha < 0.05 * dbg_ap && !use_soc) ? n_short + 1 : 0;
+        sc[S_WD_SHORT] = n_steps == 0 ? 0.0 : wd_short + 1.0;
+        sc[S_SKIP_FIRST] = 0.0;
         sc[S_MU] = mu; sc[S_NFILT] = nfilt; sc[S_THETA0] = theta0; sc[S_ACC] = acc; sc[S_ITERS] = iters + 1;
         if (trial > 0.0) sc[S_DELTA_LAST] = trial;
         sc[S_OBJ] = obj; sc[S_ERR] = err0;
@@ -1526,36 +1586,44 @@ __device__ void step_part_b(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int
 // line-search half (no model code), so it runs at twice the occupancy
 __global__ void __launch_bounds__(32 * STEP_WARPS, 4) k_step_a(Prob pr, Ws ws) {
     __shared__ WarpSm s_all[STEP_WARPS];
+    __shared__ KindTab s_tabs[NKIND];
+    build_kind_tables(pr, s_tabs, threadIdx.x, blockDim.x);
+    __syncthreads();
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int i = blockIdx.x * STEP_WARPS + wid;
     if (i >= *pr.act_count) return;
-    step_part_a(pr, ws, s_all[wid], pr.act_list[i], lane, Group{lane, 32, nullptr});
+    step_part_a(pr, ws, s_all[wid], pr.act_list[i], lane, Group{lane, 32, nullptr, s_tabs});
 }
 __global__ void __launch_bounds__(32 * STEP_WARPS, VC_STEP_MINBLOCKS) k_step_b(Prob pr, Ws ws, int* next_list, int* next_count) {
     __shared__ WarpSm s_all[STEP_WARPS];
+    __shared__ KindTab s_tabs[NKIND];
+    build_kind_tables(pr, s_tabs, threadIdx.x, blockDim.x);
+    __syncthreads();
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int i = blockIdx.x * STEP_WARPS + wid;
     if (i >= *pr.act_count) return;
     const int b = pr.act_list[i];
     if (lane == 0) ws.scal(b)[S_UPD_DIR] = 0.0;
     __syncwarp();
-    if (ws.scal(b)[S_MODE] != (double)MODE_DONE) step_part_b(pr, ws, s_all[wid], b, lane, Group{lane, 32, nullptr});
+    if (ws.scal(b)[S_MODE] != (double)MODE_DONE) step_part_b(pr, ws, s_all[wid], b, lane, Group{lane, 32, nullptr, s_tabs});
     __syncwarp();
     if (lane == 0 && ws.scal(b)[S_MODE] != (double)MODE_DONE) next_list[atomicAdd(next_count, 1)] = b;
 }
 
 // Late passes hold few instances on an otherwise idle GPU: what counts then is the latency of ONE iteration.  A whole
-// block serves one instance: warp 0 runs the unchanged scalar logic, all warps share the Riccati sweeps (one matrix
+// block serves one instance: warp 0 runs the unchanged scalar logic, four warps share the Riccati sweeps (one matrix
 // entry per thread), and in the line-search half warp w evaluates the trial point alpha = a_p 2^-w speculatively
 // before warp 0 applies the unchanged acceptance logic to the cached values (same first acceptable alpha).  Every
 // number is produced by the same arithmetic as in the warp-per-instance kernels: results are identical.
-constexpr int WIDE_A = 128;
-__global__ void __launch_bounds__(WIDE_A, 4) k_step_a_wide(Prob pr, Ws ws) {
+__global__ void __launch_bounds__(WIDE_NT, 4) k_step_a_wide(Prob pr, Ws ws) {
     __shared__ WarpSm s_one;
     __shared__ GroupCmd s_cmd;
+    __shared__ KindTab s_tabs[NKIND];
     if ((int)blockIdx.x >= *pr.act_count) return;
+    build_kind_tables(pr, s_tabs, threadIdx.x, blockDim.x);
+    __syncthreads();
     const int b = pr.act_list[blockIdx.x];
-    const Group g{(int)threadIdx.x, WIDE_A, &s_cmd};
+    const Group g{(int)threadIdx.x, WIDE_NT, &s_cmd, s_tabs};
     if (threadIdx.x < 32) {
         step_part_a(pr, ws, s_one, b, threadIdx.x, g);
         group_release(g);
@@ -1567,11 +1635,13 @@ constexpr int LS_TRIALS = 12;
 __global__ void __launch_bounds__(32 * LS_TRIALS, 1) k_step_b_wide(Prob pr, Ws ws, int* next_list, int* next_count) {
     __shared__ WarpSm s_one;
     __shared__ GroupCmd s_cmd;
+    __shared__ KindTab s_tabs[NKIND];
     __shared__ TrialCache s_trial[LS_TRIALS];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     if ((int)blockIdx.x >= *pr.act_count) return;
+    build_kind_tables(pr, s_tabs, threadIdx.x, blockDim.x);
     const int b = pr.act_list[blockIdx.x];
-    const Group g{(int)threadIdx.x, 32 * LS_TRIALS, &s_cmd};
+    const Group g{(int)threadIdx.x, WIDE_NT, &s_cmd, s_tabs};
     const double* sc = ws.scal(b);
     const bool live = sc[S_MODE] != (double)MODE_DONE;
     const bool search = live && (int)sc[S_PHASE] == PH_SEARCH;
@@ -1583,6 +1653,7 @@ __global__ void __launch_bounds__(32 * LS_TRIALS, 1) k_step_b_wide(Prob pr, Ws w
         if (lane == 0) s_trial[wid] = TrialCache{okv ? 1.0 : 0.0, ft, tht, lnt};
     }
     __syncthreads();
+    if (threadIdx.x >= WIDE_NT) return;                 // the second-order-correction sweeps are shared by four warps
     if (wid != 0) { group_helpers(pr, ws, s_one, b, g); return; }
     if (lane == 0) ws.scal(b)[S_UPD_DIR] = 0.0;
     __syncwarp();
@@ -1621,6 +1692,16 @@ __global__ void __launch_bounds__(128) k_update(Prob pr, Ws ws) {
     }
 }
 
+// instances still unfinished when the pass bound is reached: written back as they are, status VC_MAX_ITER
+__global__ void __launch_bounds__(128) k_finalize_survivors(Prob pr, Ws ws) {
+    const int lane = threadIdx.x & 31;
+    const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (i >= *pr.act_count) return;
+    const int b = pr.act_list[i];
+    const double* sc = ws.scal(b);
+    if (sc[S_MODE] != (double)MODE_DONE) finalize(pr, ws, b, lane, VC_MAX_ITER, sc[S_OBJ], sc[S_ERR]);
+}
+
 // k_nmpc_eval: objective / max equality violation / min inequality margin of given trajectories (no solve)
 __global__ void __launch_bounds__(128) k_nmpc_eval(Prob pr, const double* X, const double* U, double* out) {
     const int lane = threadIdx.x & 31;
@@ -1657,8 +1738,8 @@ static int fill_prob(vc_handle* h, Prob& pr, int B, const double* d_x0, const do
     pr.p = h->params; pr.c = h->cfg;
     pr.B = B; pr.N = h->cfg.N; pr.M = h->cfg.M; pr.H = pr.N + pr.M;
     pr.n_obs = (h->cfg.obstacles && d_obst) ? n_obs : 0;
-    pr.stall_iters = h->cfg.stall_iters; pr.restore_check = h->cfg.restore_check; pr.max_damp = h->cfg.max_damp;
-    pr.giveup_iters = h->cfg.giveup_iters; pr.max_soc = h->cfg.max_soc; pr.restore_iters = h->cfg.restore_iters;
+    pr.max_damp = h->cfg.max_damp; pr.max_soc = h->cfg.max_soc;
+    pr.watchdog_trigger = h->cfg.watchdog_trigger; pr.watchdog_trials = h->cfg.watchdog_trials;
     {   // warm-started solves may enter the monotone barrier ladder a few rungs down (option, default off)
         double mu0 = h->cfg.mu_init;
         const double mu_floor = h->cfg.tol / 11.0;
@@ -1721,7 +1802,9 @@ int launch_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_k
     k_prepare<<<(B * pr.H + 127) / 128, 128, 0, st>>>(pr, ws, lists[0], counts[0]);
     h->launches++;
     int cur = 0, n_act = B;
-    const int max_pass = h->cfg.max_iter + 16;
+    // passes that do not count as iterations: initialisation (<= 3 with re-initialisations), the final test, one per
+    // watchdog restore (at most one in watchdog_trigger + 1 iterations); survivors of the bound are finalised below
+    const int max_pass = h->cfg.max_iter + h->cfg.max_iter / 8 + 32;
     const bool debug = getenv("VC_DEBUG") != nullptr;
     int pass = 0;
     const bool prof = h->profiling != 0;
@@ -1745,7 +1828,7 @@ int launch_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_k
         cudaMemsetAsync(counts[1 - cur], 0, sizeof(int), st);
         mark();
         if (n_act <= wide_max) {
-            k_step_a_wide<<<n_act, WIDE_A, 0, st>>>(pr, ws);
+            k_step_a_wide<<<n_act, WIDE_NT, 0, st>>>(pr, ws);
             if (trace) mark();
             k_step_b_wide<<<n_act, 32 * LS_TRIALS, 0, st>>>(pr, ws, lists[1 - cur], counts[1 - cur]);
         } else {
@@ -1772,6 +1855,11 @@ int launch_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_k
             n_act = *h->h_active;
             if (n_act == 0) break;
         }
+    }
+    if (n_act > 0) {   // pass bound reached with instances left
+        pr.act_list = lists[cur]; pr.act_count = counts[cur];
+        k_finalize_survivors<<<(n_act * 32 + 127) / 128, 128, 0, st>>>(pr, ws);
+        h->launches++;
     }
     h->last_passes = pass < max_pass ? pass + 1 : max_pass;
     if (prof) {
