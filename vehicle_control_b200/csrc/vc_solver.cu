@@ -35,7 +35,8 @@ enum WsArray {
     W_V1,        // [10] Jc^T (1/s)
     W_V2,        // [10] Jc^T (z c / s)
     W_OBS,       // [8]  obstacle term: value, d/ds, d/dey, ss, s-ey, ey-ey; [6],[7] = slew weights tying u_k to u_{k-1}
-    W_AUX,       // [2]  Riccati pre-pass: direction of s at this stage; cost-to-go gradient of t of the NEXT stage
+    W_AUX,       // [10] Riccati pre-pass: direction of s at this stage; cost-to-go gradient of t of the NEXT stage;
+                 //      [2..9] second-order correction: Jc^T sigma (c_soc - (c - s)) per active variable (soc_residual)
     W_GRES,      // [8]  equality residual of the row block that defines x_k
     W_KM,        // [24] feedback gains K[2][10], kff[2]
     W_PV,        // [10] Riccati cost-to-go gradient
@@ -67,7 +68,7 @@ enum WsArray {
 struct WsTable { int width[W_COUNT + 1]; int off[W_COUNT + 1]; };
 constexpr WsTable make_ws_table() {
     WsTable t{};
-    const int w[W_COUNT] = {36, 80, 10, 10, 10, 8, 2, 8, 24, 10, 100, 10, 8, 10, 10, 80, 10, 10, 1, 1,
+    const int w[W_COUNT] = {36, 80, 10, 10, 10, 8, 10, 8, 24, 10, 100, 10, 8, 10, 10, 80, 10, 10, 1, 1,
                             10, 8, 10, 10, 8, 10, 8, 10, 10, 8, 10, 10, 38};
     int o = 0;
     for (int i = 0; i < W_COUNT; ++i) { t.width[i] = w[i]; t.off[i] = o; o += w[i]; }
@@ -196,7 +197,7 @@ __global__ void k_prepare(Prob pr, Ws ws, int* list0, int* count0) {
 // adjoint sweep of vc_adj.cuh in the same arithmetic (gradient of the stage Lagrangian + column a of its exact Hessian);
 // the Gauss-Newton part Jc^T (z/s) Jc is assembled from the eight Jacobian columns with warp shuffles.
 #ifndef VC_EVAL_MINBLOCKS
-#define VC_EVAL_MINBLOCKS 1
+#define VC_EVAL_MINBLOCKS 4
 #endif
 constexpr int EVAL_ST_LANES = 8;
 __global__ void __launch_bounds__(128, VC_EVAL_MINBLOCKS) k_eval_st(Prob pr, Ws ws) {
@@ -637,6 +638,9 @@ constexpr int F_AB = 0, F_GRES = 80, F_KM = F_GRES + 8, F_PV = F_KM + 24, F_PM =
 static_assert(BWD_DEPTH * BWD_SLOT <= RING_DOUBLES && FWD_DEPTH * FWD_SLOT <= RING_DOUBLES, "ring too small");
 static_assert(BWD_SLOT % 2 == 0 && FWD_SLOT % 2 == 0 && FWD_TAIL % 2 == 0, "slot alignment");
 static_assert(ws_offset(W_KM) == WS_FWD0 + 8 && ws_offset(W_PV) == WS_FWD0 + 32 && ws_offset(W_PM) == WS_FWD0 + 42, "forward slot layout");
+// right-hand-side-only backward sweep: 3 slots of  [AB .. GRES]  |  [KM PV PM[0..70)]  of the stage record
+constexpr int RHS_A = WS_BWD - ws_offset(W_AB), RHS_B = 24 + 10 + FWD_PM_USED, RHS_DEPTH = 3, RHS_SLOT = RHS_A + RHS_B;
+static_assert(RHS_DEPTH * RHS_SLOT <= RING_DOUBLES && RHS_A % 2 == 0 && RHS_B % 2 == 0, "rhs ring");
 
 // A solve step is run by a GROUP of NT threads per instance: one warp (NT = 32, four instances per block) while the
 // batch is large, four warps (NT = 128, named barrier) once few instances are left and latency is what counts.
@@ -733,6 +737,17 @@ __device__ __forceinline__ void stage_fetch_bwd(const double* rec0, WarpSm& sm, 
         const double* rec = rec0 + k * WS_PER_STAGE;
         double* dst = sm.ring + (k % BWD_DEPTH) * BWD_SLOT;
         for (int c = rank; c < WS_BWD / 2; c += nt) cp_async16(dst + 2 * c, rec + 2 * c);
+    }
+    cp_async_commit();
+}
+__device__ __forceinline__ void stage_fetch_rhs(const double* rec0, WarpSm& sm, int k, int rank, int nt) {
+    if (k >= 0) {
+        const double* rec = rec0 + k * WS_PER_STAGE;
+        double* dst = sm.ring + (k % RHS_DEPTH) * RHS_SLOT;
+        for (int c = rank; c < (RHS_A + RHS_B) / 2; c += nt) {
+            const bool a = c < RHS_A / 2;
+            cp_async16(dst + 2 * c, rec + (a ? O_AB + 2 * c : O_KM + 2 * (c - RHS_A / 2)));
+        }
     }
     cp_async_commit();
 }
@@ -916,7 +931,7 @@ __device__ __forceinline__ double warp_scan_down(double v, int lane) {
 // Returns false when some reduced Hessian block is not positive definite (wrong inertia for this delta).
 // The per-stage blocks are streamed through a shared-memory ring with cp.async, several stages ahead of the math;
 // every stage matrix is assembled by table-driven copies out of the staged block (KindTab).
-template <int NT>
+template <int NT, bool RHS>
 __device__ __noinline__ bool riccati(const Prob& pr, const Ws& ws, WarpSm& sm, const KindTab* tabs, int b, int rank, double mu, double delta, bool soc) {
     const int H = pr.H, N = pr.N;
     // second-order correction: same matrix, residuals replaced by the accumulated c_soc (IPOPT 2.4 / Alg. A-5.7)
@@ -951,18 +966,25 @@ __device__ __noinline__ bool riccati(const Prob& pr, const Ws& ws, WarpSm& sm, c
         }
     }
     gsync<NT>();
-    for (int j = 1; j <= BWD_DEPTH; ++j) stage_fetch_bwd(rec0, sm, H - j, rank, NT);
-    cp_async_wait<BWD_DEPTH - 1>();
+    if (RHS) {
+        for (int j = 1; j <= RHS_DEPTH; ++j) stage_fetch_rhs(rec0, sm, H - j, rank, NT);
+        cp_async_wait<RHS_DEPTH - 1>();
+    } else {
+        for (int j = 1; j <= BWD_DEPTH; ++j) stage_fetch_bwd(rec0, sm, H - j, rank, NT);
+        cp_async_wait<BWD_DEPTH - 1>();
+    }
     gsync<NT>();
     for (int k = H - 1; k >= 0; --k) {
         const KindTab& T = tabs[stage_kind(k, N, H)];
         const int n = T.n, nn = T.nn, nxr = T.nxr;
-        const double* sb = sm.ring + (k % BWD_DEPTH) * BWD_SLOT;
+        // staged block of this stage; in the right-hand-side sweep the slot starts at AB and carries the stored factors
+        const double* sb = RHS ? sm.ring + (k % RHS_DEPTH) * RHS_SLOT - O_AB : sm.ring + (k % BWD_DEPTH) * BWD_SLOT;
+        const double* sf_k = sm.ring + (k % RHS_DEPTH) * RHS_SLOT + RHS_A;   // RHS: KM | PV | PM of this stage
         double* rec = rec0 + k * WS_PER_STAGE;
         {   // ---- assemble G (stage Hessian over [x^ | p | u] + closed-form parts), M, the linear term g
             const double* ob = sb + O_OBS;
             const double cc0 = 2.0 * sf * ob[6], cc1 = 2.0 * sf * ob[7], eyey = sf * ob[5];
-            for (int e = rank; e < T.ng; e += NT) {
+            for (int e = rank; !RHS && e < T.ng; e += NT) {
                 const int src = T.gsrc[e], fl = T.gflag[e];
                 double v = src >= 0 ? sb[src] : 0.0;
                 if (fl) {
@@ -984,18 +1006,48 @@ __device__ __noinline__ bool riccati(const Prob& pr, const Ws& ws, WarpSm& sm, c
             if (a >= 0 && a < nxr + 2) {
                 const int yi = yidx(T.st != 0, a);
                 double f = sb[O_RD + yi] - mu * sb[O_V1 + yi] + sb[O_V2 + yi];
-                if (soc) {   // + Jc^T sigma (c_soc - (c - s))
-                    const double *jc = rec + O_JC, *cs = rec + O_CS, *cr = rec + O_CRES;
-                    const double *sl = rec + O_S, *z = rec + O_Z;
-                    for (int j = 0; j < (T.st ? NI_ST : NI_PM); ++j)
-                        f += jc[j * 8 + a] * (z[j] / sl[j]) * (cs[j] - (cr[j] - sl[j]));
-                }
+                if (soc) f += sb[O_AUX + 2 + a];   // + Jc^T sigma (c_soc - (c - s)), prepared by soc_residual
                 if (yi == (T.st ? IEY : QEY)) f += sf * ob[4] * sb[O_AUX];            // obstacle cross term (s, ey) x ds
                 if (T.has_next) f += sb[O_AB + T.trow * 8 + a] * sb[O_AUX + 1];       // d t_{k+1} / d a x cost-to-go of t
                 sm.g[a < nxr ? a : n + (a - nxr)] = f;
             } else if (a >= nxr + 2 && a < n + 2) sm.g[a - 2] = 0.0;                  // lifted variables: no linear term
         }
         gsync<NT>();
+        if (RHS) {
+            // ---- right-hand-side-only sweep on the stored factors: g~ = g + M^T (P r + p), kff = -R^-1 g~_u, p = g~_x + K^T g~_u
+            if (T.has_next) {
+                const int dnn = T.dnn;
+                const int q = rank - (NT - 16);
+                if (q >= 0 && q < dnn) {
+                    double a = sm.p[q];
+                    for (int l = 0; l < dnn; ++l) a += sm.P[q * 10 + l] * sm.r[l];
+                    sm.tv[q] = a;
+                }
+                gsync<NT>();
+                if (rank < nn) {
+                    double a = 0.0;
+                    for (int l = 0; l < dnn; ++l) a += sm.M[l * 12 + rank] * sm.tv[l];
+                    sm.g[rank] += a;
+                }
+                gsync<NT>();
+            }
+            const double gu0 = sm.g[n], gu1 = sm.g[n + 1];
+            const double i00 = sf_k[22], i01 = sf_k[23], i11 = sf_k[9];
+            if (rank == 31) { rec[O_KM + 20] = -(i00 * gu0 + i01 * gu1); rec[O_KM + 21] = -(i01 * gu0 + i11 * gu1); }
+            const int q = rank - (NT - 16);
+            if (q >= 0 && q < n) {
+                const double v = sm.g[q] + sf_k[q] * gu0 + sf_k[10 + q] * gu1;
+                sm.p[q] = v;
+                rec[O_PV + q] = v;
+            }
+            for (int e = rank; e < n * 10; e += NT) sm.P[e] = sf_k[34 + e];   // this stage's cost-to-go Hessian, for stage k - 1
+            const int q2 = rank - (NT - 32);
+            if (q2 >= 0 && q2 < 12) sm.r[q2] = q2 < nxr ? -(soc ? rec[o_gres + yidx(T.st != 0, q2)] : sb[O_GRES + yidx(T.st != 0, q2)]) : 0.0;
+            cp_async_wait<RHS_DEPTH - 2>();
+            gsync<NT>();
+            stage_fetch_rhs(rec0, sm, k - RHS_DEPTH, rank, NT);
+            continue;
+        }
         if (T.has_next) {
             // G += M^T P M, g += M^T (P r + p): register-blocked for the stage shapes of the shipped controllers
             const int dnn = T.dnn;
@@ -1022,7 +1074,7 @@ __device__ __noinline__ bool riccati(const Prob& pr, const Ws& ws, WarpSm& sm, c
             const double g0 = sm.G[n * 12 + rank], g1 = sm.G[(n + 1) * 12 + rank];
             km[rank] = -(i00 * g0 + i01 * g1); km[10 + rank] = -(i01 * g0 + i11 * g1);
         }
-        if (rank == 31) { km[20] = f0; km[21] = f1; }
+        if (rank == 31) { km[20] = f0; km[21] = f1; km[22] = i00; km[23] = i01; km[9] = i11; }   // n <= 8: slot 9 is free
         double* pm = rec + O_PM;
         double* pv = rec + O_PV;
         const int rcp_n = 65536 / n + 1;
@@ -1160,22 +1212,30 @@ __device__ __noinline__ bool riccati(const Prob& pr, const Ws& ws, WarpSm& sm, c
 // ---- helper threads of a block-wide group: warp 0 runs the (scalar) interior-point logic of its instance and calls
 // the others in for the factorisations.  Commands go through shared memory, hand-over by the named barrier.
 constexpr int WIDE_NT = 128;
-enum GroupOp { OP_EXIT = 0, OP_RICCATI = 1 };
+enum GroupOp { OP_EXIT = 0, OP_RICCATI = 1, OP_RICCATI_RHS = 2 };
 struct GroupCmd { int op, soc; double mu, delta; };
 struct Group { int rank, nt; GroupCmd* cmd; const KindTab* tabs; };   // cmd == nullptr for a warp group
 
 __device__ __forceinline__ bool riccati_call(const Prob& pr, const Ws& ws, WarpSm& sm, int b, const Group& g, double mu, double delta, bool soc) {
-    if (g.nt == 32) return riccati<32>(pr, ws, sm, g.tabs, b, g.rank, mu, delta, soc);
+    if (g.nt == 32) return riccati<32, false>(pr, ws, sm, g.tabs, b, g.rank, mu, delta, soc);
     if (g.rank == 0) { g.cmd->op = OP_RICCATI; g.cmd->soc = soc; g.cmd->mu = mu; g.cmd->delta = delta; }
     gsync<WIDE_NT>();   // releases the helpers (group_helpers)
-    return riccati<WIDE_NT>(pr, ws, sm, g.tabs, b, g.rank, mu, delta, soc);
+    return riccati<WIDE_NT, false>(pr, ws, sm, g.tabs, b, g.rank, mu, delta, soc);
+}
+// new right-hand side (second-order correction) on the factors the last riccati_call of this iterate stored
+__device__ __forceinline__ bool riccati_rhs_call(const Prob& pr, const Ws& ws, WarpSm& sm, int b, const Group& g, double mu, bool soc) {
+    if (g.nt == 32) return riccati<32, true>(pr, ws, sm, g.tabs, b, g.rank, mu, 0.0, soc);
+    if (g.rank == 0) { g.cmd->op = OP_RICCATI_RHS; g.cmd->soc = soc; g.cmd->mu = mu; g.cmd->delta = 0.0; }
+    gsync<WIDE_NT>();
+    return riccati<WIDE_NT, true>(pr, ws, sm, g.tabs, b, g.rank, mu, 0.0, soc);
 }
 __device__ __forceinline__ void group_helpers(const Prob& pr, const Ws& ws, WarpSm& sm, int b, const Group& g) {
     for (;;) {
         gsync<WIDE_NT>();
         const GroupCmd c = *g.cmd;
         if (c.op == OP_EXIT) return;
-        riccati<WIDE_NT>(pr, ws, sm, g.tabs, b, g.rank, c.mu, c.delta, c.soc != 0);
+        if (c.op == OP_RICCATI_RHS) riccati<WIDE_NT, true>(pr, ws, sm, g.tabs, b, g.rank, c.mu, c.delta, c.soc != 0);
+        else riccati<WIDE_NT, false>(pr, ws, sm, g.tabs, b, g.rank, c.mu, c.delta, c.soc != 0);
     }
 }
 __device__ __forceinline__ void group_release(const Group& g) {   // called by warp 0 when its instance's step is finished
@@ -1265,6 +1325,15 @@ __device__ __noinline__ void soc_residual(const Prob& pr, const Ws& ws, int b, i
         const double *cr = ws.at(b, W_CRES, k), *s = ws.at(b, W_S, k);
         for (int i = 0; i < (st ? 8 : 5); ++i) gs[i] = alpha * (first ? gr[i] : gs[i]) + gt[i];
         for (int j = 0; j < (st ? NI_ST : NI_PM); ++j) cs[j] = alpha * (first ? cr[j] - s[j] : cs[j]) + ct[j];
+        // linear-term correction of the corrected system, per active variable: Jc^T sigma (c_soc - (c - s))
+        const double *jc = ws.at(b, W_JC, k), *z = ws.at(b, W_Z, k);
+        double v3[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        for (int j = 0; j < (st ? NI_ST : NI_PM); ++j) {
+            const double w = (z[j] / s[j]) * (cs[j] - (cr[j] - s[j]));
+            for (int a = 0; a < (st ? 8 : 5); ++a) v3[a] += jc[j * 8 + a] * w;
+        }
+        double* aux = ws.at(b, W_AUX, k);
+        for (int a = 0; a < 8; ++a) aux[2 + a] = v3[a];
     }
     __syncwarp();
 }
@@ -1515,7 +1584,7 @@ __device__ void step_part_b(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int
                 soc_residual(pr, ws, b, lane, alpha, false, true);
                 double theta_soc_old = tht;   // IPOPT compares every correction with the previous TRIAL point's violation
                 for (int ps = 0; ps < pr.max_soc; ++ps) {
-                    if (!riccati_call(pr, ws, sm, b, g, mu, trial, true)) break;
+                    if (!riccati_rhs_call(pr, ws, sm, b, g, mu, true)) break;
                     double a_p2, a_d2, dphi2, ft2, tht2, lnt2;
                     slack_directions(pr, ws, b, lane, mu, tau, true, a_p2, a_d2, dphi2);
                     const bool ok2 = trial_point(pr, ws, b, lane, a_p2, true, true, ft2, tht2, lnt2);
