@@ -3,13 +3,15 @@
     python bench.py --gpus 1 --steps K --warmup W [--workload nmpc|rollout] [--impl reference]
 
 Workloads (BASELINE.json configs):
-  nmpc     cascaded 20+35 NMPC with obstacles on ippodromo, one `command()`-equivalent batched solve per
-           step from the warm start of the un-perturbed closed-loop tick (config C3; default once built)
-  rollout  SingleTrack spatial RK4 rollout + [A|B] Jacobians, N=50 (config C5)
+  nmpc     cascaded 20+35 NMPC with obstacles on ippodromo, batch 65,536: one `command()`-equivalent batched solve per
+           step from the warm start of the un-perturbed closed-loop tick (config C3; the default line, which also
+           carries the C5 numbers under "secondary.rollout")
+  rollout  SingleTrack spatial RK4 rollout + [A|B] Jacobians, 1M trajectories x N=50 (config C5)
   c2       cascaded 20+15, 4,096 perturbed instances: warm-started and cold-started solves (config C2)
 A "step" is one pass of the hot path over one batch.  `value` is device-resident throughput (CUDA events
 on the launch stream), `e2e` goes through the host-buffer C-ABI call with H2D/D2H inside the timed region.
-The instances shard across ranks with no data-path collective (weak scaling: per-GPU batch is fixed).
+--scaling strong (default): the configuration's batch is cut into contiguous shards, one per GPU, and the per-instance
+results are all-gathered (NCCL) inside the timed step; --scaling weak: every GPU gets the whole batch, no collective.
 """
 from __future__ import annotations
 
@@ -42,6 +44,8 @@ def parse():
     ap.add_argument("--scaling", default="strong", choices=["strong", "weak"],
                     help="strong: the configuration's batch is split over the GPUs; weak: every GPU gets the whole batch")
     ap.add_argument("--lap-cache", default=None, help="npz file to save/load the untimed warm-start lap (profiling runs)")
+    ap.add_argument("--rollout-batch", type=int, default=0, help="trajectories of the C5 leg (0 = 1,048,576)")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the C5 block of the default line")
     return ap.parse_args()
 
 
@@ -64,6 +68,14 @@ def main():
     else:
         from bench_nmpc import run_nmpc
         line = run_nmpc(a, rank, world, local)
+        if not a.no_secondary and a.workload is None:
+            # the second half of BASELINE.json's metric ("rollout+Jacobian states/sec") in the same driver-run record
+            import gc
+            gc.collect(); torch.cuda.empty_cache()
+            from bench_rollout import run_rollout
+            r = run_rollout(a, rank, world, local, steps=min(a.steps, 3), warmup=3)
+            line["secondary"] = {"rollout": {k: r[k] for k in ("metric", "value", "unit", "ms_per_step", "steps", "warmup", "scaling",
+                                                                "config", "e2e", "roofline", "gpu_launches", "clocks", "cpu_baseline") if k in r}}
     if rank == 0:
         print(json.dumps(line), flush=True)
     bc.dist_teardown()

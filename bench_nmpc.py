@@ -96,7 +96,7 @@ def make_batch(lap, track, B, seed, cfg):
 # algorithmic flops of one interior-point iteration (SURVEY 8d convention: one flop per add/mul/div/sqrt/
 # compare-select/elementary function): N*(F_st_eval + F_ric) + M*(F_pm_eval + F_ric5)
 def flops_per_iteration(N, M):
-    return N * (15.0e3 + 4.0e3) + M * (0.5e3 + 1.5e3)
+    return N * (15.0e3 + 4.0e3) + M * (0.5e3 + 1.5e3)   # SURVEY 8(d) convention (full-state Riccati: 4 k / 1.5 k per stage)
 
 
 # algorithmic bytes of the two dominant kernels (doubles moved per unit)
@@ -116,51 +116,38 @@ def bytes_per_solve(H):
     return 8.0 * ((8 + H + H + 10 * H) + (10 * H + 3))
 
 
-def cpu_baseline_nmpc(lap, track_yaml, cfg, seconds=25.0, procs=1):
-    """The CPU oracle (oracle/nlp.py + oracle/ipm.py: numpy/torch restatement of CasADi+IPOPT) solving warm-started
-    ticks of the same workload, `procs` single-threaded processes."""
-    import multiprocessing as mp
-    ticks = [int(t) for t in np.linspace(1, len(lap["x0"]) - 1, max(procs, 1) * 4).astype(int)]
-    args = [(track_yaml, cfg, lap["x0"][t], lap["Xw"][t], lap["Uw"][t]) for t in ticks]
-    t0 = time.perf_counter()
-    done = 0
-    if procs <= 1:
-        for a in args:
-            done += _oracle_solve(a)
-            if time.perf_counter() - t0 > seconds:
-                break
-    else:
-        with mp.get_context("spawn").Pool(procs) as pool:
-            for r in pool.imap_unordered(_oracle_solve, args[:procs * 2]):
-                done += r
-    el = time.perf_counter() - t0
-    return {"value": done / el, "unit": "solves/s", "cores": procs, "kind": "port",
-            "sample": f"{done} warm-started ticks of the same lap (loop capped at 30 iterations) solved by the CPU oracle in {el:.1f} s "
-                      f"({procs} single-threaded process(es)); the reference's own logs report 14-25 solves/s "
-                      f"(IPOPT+MA27, 1 thread, BASELINE.md)"}
+def source_hash():
+    """hash of the CUDA sources the ncu per-unit numbers (profiles/*_ncu_units.json) were captured for"""
+    import hashlib
+    h = hashlib.sha256()
+    d = os.path.join(bc.ROOT, "vehicle_control_b200", "csrc")
+    for f in sorted(os.listdir(d)):
+        with open(os.path.join(d, f), "rb") as fh:
+            h.update(fh.read())
+    return h.hexdigest()[:16]
 
 
-def _oracle_solve(a):
-    import torch
-    torch.set_num_threads(1)
-    from oracle import ipm, models as om, nlp as on
-    from oracle.track import OracleTrack
-    track_yaml, cfg, x0, Xw, Uw = a
-    tr = OracleTrack(track_yaml)
-    c = on.MpcCfg.from_config(cfg)
-    ds, kap = on.horizon_params(c, tr, x0, Xw[0])
-    obst = np.array([o[:3] for o in tr.obstacles]) if c.obstacles else None
-    p = on.NLP(c, om.DEFAULT, x0, kap, ds, obst)
-    # bounded work: interior-point loop capped at 30 iterations, a capped solve still counts (favours the CPU figure)
-    ipm.solve(p, p.pack(Xw, Uw), ipm.IpmOptions(max_iter=30, max_restorations=0))
-    return 1
+def ncu_units():
+    """per-unit DRAM bytes / executed flops of the kernels from the newest committed ncu capture, with a staleness flag"""
+    import glob
+    import json
+    files = sorted(glob.glob(os.path.join(bc.ROOT, "profiles", "r*_ncu_units.json")))
+    if not files:
+        return None
+    with open(files[-1]) as f:
+        u = json.load(f)
+    u["file"] = os.path.relpath(files[-1], bc.ROOT)
+    u["stale"] = u.get("source_hash") != source_hash()
+    return u
 
 
 def run_nmpc(a, rank, world, local):
     import torch
+    from vehicle_control_b200 import sharding
     from vehicle_control_b200.engine import Engine
     from vehicle_control_b200.environment.track import Track
-    B = a.batch or 65536
+    strong = a.scaling == "strong"
+    B_total = (a.batch or 65536) * (1 if strong else world)
     cfg = controller_config()
     track_yaml = bc.load_yaml("environment/ippodromo.yaml")
     tr = Track(track_yaml)
@@ -176,17 +163,27 @@ def run_nmpc(a, rank, world, local):
         if cache and rank == 0:
             np.savez(cache, **lap)
     lap_s = time.perf_counter() - t0
-    x0h, Xwh, Uwh, obh, _ = make_batch(lap, tr, B, SEED + rank, cfg)
+    if strong:   # the configuration's batch, cut into contiguous shards (every rank builds the same batch)
+        x0h, Xwh, Uwh, obh, _ = make_batch(lap, tr, B_total, SEED, cfg)
+        lo, hi = sharding.shard_range(B_total, rank, world)
+        x0h, Xwh, Uwh, obh = x0h[lo:hi], Xwh[lo:hi], Uwh[lo:hi], obh[lo:hi]
+    else:
+        x0h, Xwh, Uwh, obh, _ = make_batch(lap, tr, B_total // world, SEED + rank, cfg)
+    B = len(x0h)
     x0, Xw, Uw, ob = eng.tensor(x0h), eng.tensor(Xwh), eng.tensor(Uwh), eng.tensor(obh)
     X, U = torch.empty_like(Xw), torch.empty_like(Uw)
     ds, kap = eng.empty(B, H), eng.empty(B, H)
     out = {"obj": eng.empty(B), "status": eng.empty(B, dtype=torch.int32), "iters": eng.empty(B, dtype=torch.int32),
            "kkt": eng.empty(B)}
+    gathered = {}
 
     def step():
         X.copy_(Xw); U.copy_(Uw)                      # the warm start (solve is in place)
         eng.horizon_params(x0, X, ds, kap)            # _init_horizon
         eng.solve(x0, kap, ds, X, U, obstacles=ob, out=out)   # opti.solve()
+        if strong and world > 1:                       # the one collective of the design: result gather (NCCL all_gather)
+            gathered.update(sharding.gather_results({"u0": U[:, :, 0].contiguous(), "obj": out["obj"],
+                                                     "status": out["status"], "iters": out["iters"]}, B_total))
 
     eng.set_profiling(True)
     l0 = eng.launch_count()
@@ -196,37 +193,38 @@ def run_nmpc(a, rank, world, local):
     prof = eng.profile()
     eng.set_profiling(False)
     ms = total_ms / a.steps
-    value = world * B / (ms * 1e-3)
+    value = B_total / (ms * 1e-3)
     status, iters = out["status"].cpu().numpy(), out["iters"].cpu().numpy()
     conv = float((status <= 1).mean())
     status_hist = {str(int(k)): int(v) for k, v in zip(*np.unique(status, return_counts=True))}
     it_pct = {f"p{q}": float(np.percentile(iters, q)) for q in (50, 90, 99, 99.9)}
     mean_it = float(iters.mean())
     runs = a.steps + a.warmup
-    # ---- e2e: host buffers through vc_nmpc_solve_host (H2D + solve + D2H inside the call)
+    Ug, objg = U.cpu().numpy(), out["obj"].cpu().numpy()
+    kap_h, ds_h = kap.cpu().numpy(), ds.cpu().numpy()
+    # ---- e2e: `command()` from pinned host buffers through vc_nmpc_command_host: H2D of state, previous prediction and
+    # obstacles, _init_horizon + solve on the device, D2H of the new prediction and the per-instance results, all timed
     Be = B if a.e2e_batch == 0 else min(B, a.e2e_batch)
-
-    def pinned(arr):   # page-locked host copy (numpy view of a pinned torch tensor)
-        t = torch.from_numpy(np.ascontiguousarray(arr)).pin_memory()
-        return t, t.numpy()
-
     keep = []
-    def hp(arr):
-        t, v = pinned(arr); keep.append(t); return v
-    hx0, hkap, hds = hp(x0h[:Be]), hp(kap[:Be].cpu().numpy()), hp(ds[:Be].cpu().numpy())
-    hob = hp(obh[:Be])
-    hX, hU = hp(Xwh[:Be]), hp(Uwh[:Be])
-    eng.solve_host(hx0, hkap, hds, hX, hU, obstacles=hob)   # warm-up (allocates the staging arena)
+
+    def hp(arr):   # page-locked host copy (numpy view of a pinned torch tensor)
+        t = torch.from_numpy(np.ascontiguousarray(arr)).pin_memory()
+        keep.append(t)
+        return t.numpy()
+
+    hx0, hob, hX, hU = hp(x0h[:Be]), hp(obh[:Be]), hp(Xwh[:Be]), hp(Uwh[:Be])
+    eng.command_host(hx0, hX, hU, obstacles=hob)   # warm-up (allocates the staging arena)
     bc.barrier()
     e2e_t = 0.0
-    for _ in range(max(1, min(a.steps, 3))):
+    e2e_n = max(1, min(a.steps, 3))
+    for _ in range(e2e_n):
         hX[:], hU[:] = Xwh[:Be], Uwh[:Be]
         t1 = time.perf_counter()
-        eng.solve_host(hx0, hkap, hds, hX, hU, obstacles=hob)
+        eng.command_host(hx0, hX, hU, obstacles=hob)
         e2e_t += time.perf_counter() - t1
-    e2e_n = max(1, min(a.steps, 3))
     e2e_s = bc.max_over_ranks(e2e_t / e2e_n)
-    h2d = (hx0.nbytes + hkap.nbytes + hds.nbytes + hob.nbytes + hX.nbytes + hU.nbytes)
+    Be_total = int(bc.sum_over_ranks(Be))
+    h2d = hx0.nbytes + hob.nbytes + hX.nbytes + hU.nbytes
     d2h = hX.nbytes + hU.nbytes + Be * (8 + 8 + 4 + 4)
     # ---- roofline of the dominant kernel: algorithmic work / measured launch time (CUDA events on the solve stream)
     peak_hbm, how = bc.measured_peaks()
@@ -235,37 +233,43 @@ def run_nmpc(a, rank, world, local):
     share = [m / max(1e-9, sum(prof["ms"])) for m in prof["ms"]]
     inst_passes = max(1, prof["instance_passes"])          # sum over timed+warm-up passes of the active instances
     fp64_peak = bc.FP64_PEAK_TFLOPS
-    # units per launch: one launch of k_step (the pair k_step_a -> k_step_b, timed together with CUDA events on the
+    nu = ncu_units() or {}
+    # units per launch: one launch of k_step (k_step_a -> k_step_b -> k_update, timed together with CUDA events on the
     # solve stream) advances every unfinished instance by one interior-point iteration; one launch of k_eval_st
-    # evaluates N stages of every unfinished instance.  ncu_dram_bytes_per_unit: from
-    # profiles/r01_ncu_split_kernels.md (k_step_a 413.8 KB + k_step_b 103.8 KB per instance-iteration)
+    # evaluates N stages of every unfinished instance
     kern = {
         "k_step": {"units_per_launch": inst_passes / n_step, "unit": "instance-iteration", "bytes_per_unit": STEP_BYTES(H),
-                   "flops_per_unit": N * 4.0e3 + M * 1.5e3 + (N * 0.73e3 + M * 0.1e3), "launch_ms": ms_step / n_step,
-                   "ncu_dram_bytes_per_unit": 517.6e3, "executed_flops_per_unit": 458.4e3},
+                   "flops_per_unit": N * 2.0e3 + M * 0.8e3 + (N * 0.73e3 + M * 0.1e3), "launch_ms": ms_step / n_step,
+                   "ncu_dram_bytes_per_unit": (nu.get("k_step") or {}).get("dram_bytes_per_unit"),
+                   "executed_flops_per_unit": (nu.get("k_step") or {}).get("executed_flops_per_unit")},
         "k_eval_st": {"units_per_launch": inst_passes * N / n_st, "unit": "stage evaluation", "bytes_per_unit": EVAL_ST_BYTES,
-                      "flops_per_unit": 15.0e3, "launch_ms": ms_st / n_st, "ncu_dram_bytes_per_unit": 2715.0, "executed_flops_per_unit": 222.7e3},
+                      "flops_per_unit": 15.0e3, "launch_ms": ms_st / n_st,
+                      "ncu_dram_bytes_per_unit": (nu.get("k_eval_st") or {}).get("dram_bytes_per_unit"),
+                      "executed_flops_per_unit": (nu.get("k_eval_st") or {}).get("executed_flops_per_unit")},
     }
     dom = "k_step" if ms_step >= ms_st else "k_eval_st"
     kd = kern[dom]
-    ach = kd["units_per_launch"] * kd["bytes_per_unit"] / (kd["launch_ms"] * 1e-3) / 1e9
+    per_s = lambda v, per_unit: None if per_unit is None else v["units_per_launch"] * per_unit / (v["launch_ms"] * 1e-3)
+    ach = per_s(kd, kd["bytes_per_unit"]) / 1e9
     solve_flops = mean_it * flops_per_iteration(N, M)
     roof = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak_hbm, "unit": "GB/s", "frac": ach / peak_hbm,
-            "traffic": kd["units_per_launch"] * kd["ncu_dram_bytes_per_unit"], "peak_source": how,
-            "traffic_source": "dram__bytes_read+write per unit from the committed ncu --set full capture (profiles/), "
-                              "times this run's average units per launch",
+            "traffic": None if kd["ncu_dram_bytes_per_unit"] is None else kd["units_per_launch"] * kd["ncu_dram_bytes_per_unit"],
+            "peak_source": how,
+            "traffic_source": ("dram__bytes_read+write per unit from the committed ncu --set full capture (%s%s) times this "
+                               "run's average units per launch" % (nu.get("file"), ", STALE: kernel sources changed since" if nu.get("stale") else "")
+                               if nu else "no committed ncu capture"),
             "units_per_launch": kd["units_per_launch"], "unit_of_work": kd["unit"],
             "algorithmic_bytes_per_unit": kd["bytes_per_unit"], "launch_ms": kd["launch_ms"],
             "share_of_step": share[2] if dom == "k_step" else share[0],
-            "fp64": {"achieved_tflops": kd["units_per_launch"] * kd["flops_per_unit"] / (kd["launch_ms"] * 1e-3) / 1e12,
-                     "executed_tflops": kd["units_per_launch"] * kd["executed_flops_per_unit"] / (kd["launch_ms"] * 1e-3) / 1e12,
-                     "executed_source": "DFMA x2 + DMUL + DADD thread instructions per unit from the committed ncu captures "
-                                        "(scripts/ncu_flops.py, profiles/r01_flop_counts.md) x this run's units and time",
+            "note": "the step kernels are bound by neither roof: they are latency / instruction-issue bound (sequential "
+                    "Riccati and line-search chains, DESIGN.md section 4); the HBM fraction is reported as the contract asks",
+            "fp64": {"achieved_tflops": per_s(kd, kd["flops_per_unit"]) / 1e12,
+                     "executed_tflops": None if kd["executed_flops_per_unit"] is None else per_s(kd, kd["executed_flops_per_unit"]) / 1e12,
                      "peak_tflops": fp64_peak, "peak_source": "measured DFMA micro-benchmark (profiles/r01_fp64_peak.txt)"},
             "kernels": {k: {"launch_ms": v["launch_ms"], "units_per_launch": v["units_per_launch"],
-                            "hbm_gbs": v["units_per_launch"] * v["bytes_per_unit"] / (v["launch_ms"] * 1e-3) / 1e9,
-                            "fp64_tflops": v["units_per_launch"] * v["flops_per_unit"] / (v["launch_ms"] * 1e-3) / 1e12,
-                            "fp64_executed_tflops": v["units_per_launch"] * v["executed_flops_per_unit"] / (v["launch_ms"] * 1e-3) / 1e12}
+                            "hbm_gbs": per_s(v, v["bytes_per_unit"]) / 1e9,
+                            "fp64_tflops": per_s(v, v["flops_per_unit"]) / 1e12,
+                            "fp64_executed_tflops": None if v["executed_flops_per_unit"] is None else per_s(v, v["executed_flops_per_unit"]) / 1e12}
                         for k, v in kern.items()},
             "whole_solve_fp64": {"achieved_tflops": value / world * solve_flops / 1e12,
                                  "frac": value / world * solve_flops / 1e12 / fp64_peak, "flops_per_solve": solve_flops},
@@ -273,19 +277,27 @@ def run_nmpc(a, rank, world, local):
     roof["fp64"]["frac"] = roof["fp64"]["achieved_tflops"] / fp64_peak
     line = {
         "metric": "NMPC solves/sec", "value": value, "unit": "solves/s", "n_gpus": world, "steps": a.steps,
-        "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": a.scaling, "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "C3: cascaded NMPC 20+35 with obstacles, ippodromo, warm-started perturbed instances",
-                   "batch_per_gpu": B, "N": N, "M": M, "n_obstacles": int(obh.shape[1]), "tol": 1e-8,
+        "config": {"workload": "C3: cascaded NMPC 20+35 with obstacles, ippodromo, batch 65,536 warm-started perturbed instances",
+                   "batch_total": B_total, "batch_per_gpu": B, "N": N, "M": M, "n_obstacles": int(obh.shape[1]), "tol": 1e-8,
+                   "solver": {"max_iter": MAX_ITER, "max_soc": 4, "watchdog_trigger": 10, "note": "same on the CPU arm"},
+                   "result_gather": "all_gather of (u0, obj, status, iters) inside the timed step" if strong and world > 1 else "none (one rank)" if world == 1 else "none (weak scaling)",
+                   "gathered_rows": int(gathered["obj"].shape[0]) if gathered else None,
                    "converged_frac": conv, "status_counts": status_hist, "mean_iters": mean_it, "iters_percentiles": it_pct,
                    "max_iters": int(iters.max()), "passes": int(prof["last_passes"]),
                    "lap_ticks": int(len(lap["x0"])), "lap_replay_s": lap_s,
                    "l2": "per-step working set %.1f GB (solver workspace) >> 126 MB L2" % (eng.workspace_bytes() / 1e9)},
         "clocks": clk.summary(), "gpu_launches": int(round(launches_total * a.steps / runs)),
-        "e2e": {"value": world * Be / e2e_s, "unit": "solves/s", "h2d_bytes_per_step": int(h2d),
-                "d2h_bytes_per_step": int(d2h), "batch": Be},
+        "e2e": {"value": Be_total / e2e_s, "unit": "solves/s", "h2d_bytes_per_step": int(h2d),
+                "d2h_bytes_per_step": int(d2h), "batch_per_gpu": Be,
+                "call": "vc_nmpc_command_host: H2D (state, previous prediction, obstacles), _init_horizon + solve on the device, D2H (prediction, results)"},
         "roofline": roof,
     }
     if rank == 0 and not a.no_cpu_baseline:
-        line["cpu_baseline"] = cpu_baseline_nmpc(lap, track_yaml, cfg)
+        import bench_reference as br
+        n_cpu = min(B, a.cpu_instances or 512)
+        sample = dict(x0=x0h[:n_cpu], Xw=Xwh[:n_cpu], Uw=Uwh[:n_cpu], obst=obh[:n_cpu], ds=ds_h[:n_cpu], kappa=kap_h[:n_cpu])
+        line["cpu_baseline"] = br.cpu_baseline_nmpc(cfg, sample, Ug[:n_cpu], objg[:n_cpu])
+    del X, U, Xw, Uw
     return line

@@ -150,6 +150,12 @@ int vc_nmpc_solve_host(vc_handle* h, int B, const double* h_x0, const double* h_
                        const double* h_obst, int n_obs, double* h_X, double* h_U, double* h_obj,
                        int* h_status, int* h_iters, double* h_kkt);
 
+/* replaces: CascadedMPC.command(state) for a batch, host buffers in and out (cascaded_mpc.py:306-338): _init_horizon on the
+ * device (vc_set_track must have been called), the solve, and every host<->device copy inside the call.  h_x0[B,8];
+ * h_obst[B,n_obs,3] or NULL; h_X[B,8,H] / h_U[B,2,H]: previous prediction in (the warm start), solution out.  Synchronises. */
+int vc_nmpc_command_host(vc_handle* h, int B, const double* h_x0, const double* h_obst, int n_obs, double* h_X, double* h_U,
+                         double* h_obj, int* h_status, int* h_iters, double* h_kkt);
+
 /* Measurement hooks (no reference counterpart; the reference times command() with time.time(), racing.py:231-233):
  * with profiling on, vc_nmpc_solve brackets every kernel of its iteration loop with CUDA events on the handle's
  * stream.  vc_get_profile: accumulated ms and launch counts of k_eval_st, k_eval_pm, k_step since

@@ -56,6 +56,7 @@ EXPORTS = {
     "vc_nmpc_solve": (C.c_int, [C.c_void_p, C.c_int, PD, PD, PD, PD, C.c_int, PD, PD, PD, PD, PD, PD]),
     "vc_nmpc_eval": (C.c_int, [C.c_void_p, C.c_int, PD, PD, PD, PD, C.c_int, PD, PD, PD]),
     "vc_nmpc_solve_host": (C.c_int, [C.c_void_p, C.c_int, PD, PD, PD, PD, C.c_int, PD, PD, PD, PD, PD, PD]),
+    "vc_nmpc_command_host": (C.c_int, [C.c_void_p, C.c_int, PD, PD, C.c_int, PD, PD, PD, PD, PD, PD]),
     "vc_set_profiling": (C.c_int, [C.c_void_p, C.c_int]),
     "vc_get_profile": (C.c_int, [C.c_void_p, PD, PD, PD]),
     "vc_get_profile_instance_passes": (C.c_longlong, [C.c_void_p]),

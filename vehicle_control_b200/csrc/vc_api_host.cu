@@ -64,6 +64,50 @@ int vc_nmpc_solve_host(vc_handle* h, int B, const double* h_x0, const double* h_
     return check_cuda(cudaStreamSynchronize(st), "vc_nmpc_solve_host");
 }
 
+// CascadedMPC.command() for a batch, host buffers in and out: _init_horizon on the device (needs vc_set_track), the
+// solve, and the copies, all inside the call.  h_X / h_U: previous prediction in (warm start), solution out.
+int vc_nmpc_command_host(vc_handle* h, int B, const double* h_x0, const double* h_obst, int n_obs, double* h_X, double* h_U,
+                         double* h_obj, int* h_status, int* h_iters, double* h_kkt) {
+    if (!h) { set_error("vc_nmpc_command_host: null handle"); return -1; }
+    if (B <= 0) return 0;
+    if (!h_x0 || !h_X || !h_U) { set_error("vc_nmpc_command_host: null buffer"); return -1; }
+    const int H = h->cfg.N + h->cfg.M;
+    const size_t nB = (size_t)B;
+    const size_t o_x0 = 0, o_k = o_x0 + nB * 8, o_ds = o_k + nB * H, o_ob = o_ds + nB * H,
+                 o_X = o_ob + nB * (size_t)n_obs * 3, o_U = o_X + nB * 8 * H, o_obj = o_U + nB * 2 * H,
+                 o_kkt = o_obj + nB, o_int = o_kkt + nB, total = o_int + nB;
+    const size_t bytes = total * sizeof(double);
+    cudaSetDevice(h->device);
+    if (bytes > h->scratch_bytes) {
+        cudaFree(h->d_scratch);
+        h->d_scratch = nullptr; h->scratch_bytes = 0;
+        int rc = check_cuda(cudaMalloc(&h->d_scratch, bytes), "cudaMalloc(scratch)");
+        if (rc) return rc;
+        h->scratch_bytes = bytes;
+    }
+    double* d = (double*)h->d_scratch;
+    int* d_status = (int*)(d + o_int);
+    int* d_iters = d_status + nB;
+    cudaStream_t st = h->stream;
+    const bool obst = h_obst && n_obs > 0;
+    cudaMemcpyAsync(d + o_x0, h_x0, nB * 8 * sizeof(double), cudaMemcpyHostToDevice, st);
+    if (obst) cudaMemcpyAsync(d + o_ob, h_obst, nB * n_obs * 3 * sizeof(double), cudaMemcpyHostToDevice, st);
+    cudaMemcpyAsync(d + o_X, h_X, nB * 8 * H * sizeof(double), cudaMemcpyHostToDevice, st);
+    cudaMemcpyAsync(d + o_U, h_U, nB * 2 * H * sizeof(double), cudaMemcpyHostToDevice, st);
+    int rc = vc_horizon_params(h, B, d + o_x0, d + o_X, d + o_ds, d + o_k);
+    if (rc) return rc;
+    rc = launch_nmpc_solve(h, B, d + o_x0, d + o_k, d + o_ds, obst ? d + o_ob : nullptr, n_obs, d + o_X, d + o_U, d + o_obj,
+                           d_status, d_iters, d + o_kkt);
+    if (rc) return rc;
+    cudaMemcpyAsync(h_X, d + o_X, nB * 8 * H * sizeof(double), cudaMemcpyDeviceToHost, st);
+    cudaMemcpyAsync(h_U, d + o_U, nB * 2 * H * sizeof(double), cudaMemcpyDeviceToHost, st);
+    if (h_obj) cudaMemcpyAsync(h_obj, d + o_obj, nB * sizeof(double), cudaMemcpyDeviceToHost, st);
+    if (h_kkt) cudaMemcpyAsync(h_kkt, d + o_kkt, nB * sizeof(double), cudaMemcpyDeviceToHost, st);
+    if (h_status) cudaMemcpyAsync(h_status, d_status, nB * sizeof(int), cudaMemcpyDeviceToHost, st);
+    if (h_iters) cudaMemcpyAsync(h_iters, d_iters, nB * sizeof(int), cudaMemcpyDeviceToHost, st);
+    return check_cuda(cudaStreamSynchronize(st), "vc_nmpc_command_host");
+}
+
 int vc_nmpc_debug_read(vc_handle* h, int b, int array, double* h_out, int n) {
     if (!h || !h_out) { set_error("vc_nmpc_debug_read: null argument"); return -1; }
     return debug_read(h, b, array, h_out, n);

@@ -247,6 +247,20 @@ class Engine:
                                           kkt.ctypes.data), "vc_nmpc_solve_host")
         return {"obj": obj, "status": status, "iters": iters, "kkt": kkt}
 
+    def command_host(self, x0, X, U, obstacles=None):
+        """`command()` for a batch from host buffers (numpy; X and U = previous prediction in, solution out): horizon
+        parameters, solve and all copies inside the call (include/vc_api.h: vc_nmpc_command_host)."""
+        B = x0.shape[0]
+        for a in (x0, X, U):
+            assert a.dtype == np.float64 and a.flags.c_contiguous
+        obj, kkt = np.empty(B), np.empty(B)
+        status, iters = np.empty(B, np.int32), np.empty(B, np.int32)
+        n_obs = 0 if obstacles is None else obstacles.shape[1]
+        check(self.lib.vc_nmpc_command_host(self._h, B, x0.ctypes.data, obstacles.ctypes.data if n_obs else None, n_obs,
+                                            X.ctypes.data, U.ctypes.data, obj.ctypes.data, status.ctypes.data,
+                                            iters.ctypes.data, kkt.ctypes.data), "vc_nmpc_command_host")
+        return {"obj": obj, "status": status, "iters": iters, "kkt": kkt}
+
     def set_profiling(self, on: bool):
         check(self.lib.vc_set_profiling(self._h, 1 if on else 0), "vc_set_profiling")
 
