@@ -475,7 +475,7 @@ __device__ __noinline__ StageVal stage_trial(const Prob& pr, int b, int k, const
 #define VC_STEP_WARPS 4
 #endif
 #ifndef VC_STEP_MINBLOCKS
-#define VC_STEP_MINBLOCKS 1
+#define VC_STEP_MINBLOCKS 4
 #endif
 constexpr int STEP_WARPS = VC_STEP_WARPS;
 constexpr int RING_DOUBLES = 768;
