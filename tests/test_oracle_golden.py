@@ -61,3 +61,20 @@ def test_jacobian_sanity_vector(golden, oracle_tracks):
     assert abs(J[1, 3] - 1.189958) < 1e-5 and abs(J[7, 0] + 1.745812e-03) < 1e-8
     assert abs(J[0, 8] - 1.802946e-05) < 1e-10 and abs(J[3, 9] - 3.023466e-02) < 1e-7
     assert np.array_equal(J[:, 4], np.eye(8)[4]) and np.array_equal(J[:, 7], np.eye(8)[7])
+
+
+def test_tyre_forces_match_the_reference_logs(golden):
+    """experiments/logs/*.log known answers (tests/golden/log_kat.json): block k = forces at (state[k+1], action[k+1]),
+    printed by the reference with 6 significant digits (dynamic_car.py:20-47)."""
+    import json
+    import os
+    from tests.conftest import ROOT
+    z, _ = golden
+    kat = json.load(open(os.path.join(ROOT, "tests", "golden", "log_kat.json")))
+    for key, blocks in kat.items():
+        S, A = z[key + "/state"], z[key + "/action"]
+        for k, ref in blocks.items():
+            x, u = S[int(k) + 1], A[int(k) + 1]
+            f = [om.Fx_f(np, om.DEFAULT, u[0]), om.Fx_r(np, om.DEFAULT, u[0]), om.Fy_f(np, om.DEFAULT, *x[:4], u[0]),
+                 om.Fy_r(np, om.DEFAULT, *x[:4], u[0])]
+            assert all(abs(a - b) <= 6e-6 * abs(b) + 1e-8 for a, b in zip(f, ref)), (key, k, f, ref)

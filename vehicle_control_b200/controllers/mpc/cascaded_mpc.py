@@ -72,8 +72,9 @@ class BatchedCascadedMPC(Controller):
 
     def command(self, states: torch.Tensor, active: torch.Tensor = None) -> torch.Tensor:
         """states [B,8] (device) -> first actions [B,2] (device view of action_prediction[:, :, 0]).
-        `active` [B] bool: instances whose failure is worth a retry (the lock-step simulator passes the vehicles
-        still racing)."""
+        `active` [B] bool: the instances to solve (the lock-step simulator passes the vehicles still racing); the others
+        keep their prediction and are not touched -- the active ones are compacted into a sub-batch, solved and scattered
+        back, so that finished vehicles cost nothing and cannot hold the lock-step passes."""
         e = self.engine
         # first tick: cold guess, barrier ladder from mu_init; later ticks are warm starts and may enter the ladder
         # `warm_rungs` rungs down (controller config key, default 0 = the reference's IPOPT behaviour)
@@ -82,26 +83,38 @@ class BatchedCascadedMPC(Controller):
             e.cfg.warm_rungs = rungs
             e.set_config(e.cfg)
         self._ticks += 1
-        if self.retry_failed:
-            Xw, Uw = self.state_prediction.clone(), self.action_prediction.clone()
-        e.horizon_params(states, self.state_prediction, self.ds, self.kappa, track_id=self.track_id)
-        e.solve(states, self.kappa, self.ds, self.state_prediction, self.action_prediction,
-                obstacles=self.obstacles, out=self.info)
-        if self.retry_failed:
-            self._mask = active
-            if bool(self._failed().any()):
-                self._retry(states, Xw, Uw)
+        if active is None or bool(active.all()):
+            self._solve(states, self.state_prediction, self.action_prediction, self.ds, self.kappa, self.info,
+                        self.obstacles, self.track_id)
+        else:
+            idx = active.nonzero().squeeze(1)
+            if idx.numel() == 0:
+                return self.action_prediction[:, :, 0].contiguous()
+            sub = lambda t: None if t is None else t[idx].contiguous()
+            X, U, ds, kap = sub(self.state_prediction), sub(self.action_prediction), sub(self.ds), sub(self.kappa)
+            info = {k: v[idx].contiguous() for k, v in self.info.items()}
+            self._solve(sub(states), X, U, ds, kap, info, sub(self.obstacles), sub(self.track_id))
+            self.state_prediction[idx], self.action_prediction[idx] = X, U
+            self.ds[idx], self.kappa[idx] = ds, kap
+            for k in self.info:
+                self.info[k][idx] = info[k]
         return self.action_prediction[:, :, 0].contiguous()
 
-    def _failed(self):
-        bad = self.info["status"] > 1
-        return bad if self._mask is None else bad & self._mask
+    def _solve(self, states, X, U, ds, kap, info, obstacles, track_id):
+        """_init_horizon + solve (+ the retries of failed instances) of one batch, in place in the given tensors."""
+        e = self.engine
+        if self.retry_failed:
+            Xw, Uw = X.clone(), U.clone()
+        e.horizon_params(states, X, ds, kap, track_id=track_id)
+        e.solve(states, kap, ds, X, U, obstacles=obstacles, out=info)
+        if self.retry_failed and bool((info["status"] > 1).any()):
+            self._retry(states, Xw, Uw, X, U, ds, kap, info, obstacles, track_id)
 
-    def _retry(self, states, Xw, Uw):
+    def _retry(self, states, Xw, Uw, Xs, Us, dss, kaps, info, obstacles, track_id):
         """Second and third attempt for the instances that failed, as a compacted sub-batch."""
         e, N = self.engine, self.N
         for kind in ("shifted", "cold"):
-            idx = self._failed().nonzero().squeeze(1)
+            idx = (info["status"] > 1).nonzero().squeeze(1)
             if idx.numel() == 0:
                 return
             if kind == "shifted":    # SingleTrack columns advance by one stage; the PointMass tail stays
@@ -112,22 +125,20 @@ class BatchedCascadedMPC(Controller):
                 X = self._cold[0].repeat(idx.numel(), 1, 1)
                 U = self._cold[1].repeat(idx.numel(), 1, 1)
             x = states[idx].contiguous()
-            ds, kap = e.horizon_params(x, X, track_id=None if self.track_id is None else self.track_id[idx].contiguous())
-            ob = self.obstacles[idx].contiguous() if self.obstacles is not None else None
+            ds, kap = e.horizon_params(x, X, track_id=None if track_id is None else track_id[idx].contiguous())
+            ob = obstacles[idx].contiguous() if obstacles is not None else None
             out = e.solve(x, kap, ds, X, U, obstacles=ob)
             ok = out["status"] <= 1
             self.retries[kind] += int(ok.sum())
             good = idx[ok]
-            self.state_prediction[good] = X[ok]
-            self.action_prediction[good] = U[ok]
-            self.ds[good], self.kappa[good] = ds[ok], kap[ok]
-            for k in self.info:
-                self.info[k][good] = out[k][ok]
-        bad = self._failed()
+            Xs[good], Us[good] = X[ok], U[ok]
+            dss[good], kaps[good] = ds[ok], kap[ok]
+            for k in info:
+                info[k][good] = out[k][ok]
+        bad = info["status"] > 1
         self.retries["unrecovered"] += int(bad.sum())
         # nothing converged for these: keep the warm start they had (not the failed iterate) for the next tick
-        self.state_prediction[bad] = Xw[bad]
-        self.action_prediction[bad] = Uw[bad]
+        Xs[bad], Us[bad] = Xw[bad], Uw[bad]
 
     def get_state_prediction(self) -> torch.Tensor:
         """[B,H,3] global (x, y, psi) of every predicted state (:340-352)."""

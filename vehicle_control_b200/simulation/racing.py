@@ -228,3 +228,81 @@ class BatchedRacingSimulator:
 
     def laptimes(self):
         return self.x[:, 7].cpu().numpy()
+
+    # ------------------------------------------------------------------ persistence / summary (racing.py:441-459, 92-106)
+    def _trajectories(self):
+        """state_traj [T+1,B,8], action_traj [T+1,B,2] with the reference's zero placeholder in row 0 (racing.py:79-84)."""
+        if not self.record:
+            raise RuntimeError("BatchedRacingSimulator(record=False) keeps no trajectories")
+        st = torch.stack(self.state_traj).cpu().numpy()
+        ac = torch.stack([torch.zeros_like(self.action_traj[0])] + self.action_traj).cpu().numpy() if self.action_traj \
+            else np.zeros((1, self.B, 2))
+        return st, ac
+
+    def save(self, data_dir, name="batched"):
+        """One compressed `{name}_batched.npz` for all vehicles (+ `{name}_config.yaml`): state_traj [T+1,B,8],
+        action_traj [T+1,B,2], ticks [B] (rows 0..ticks[b] of vehicle b are its lap), failed [B]."""
+        os.makedirs(data_dir, exist_ok=True)
+        st, ac = self._trajectories()
+        np.savez_compressed(os.path.join(data_dir, f"{name}_batched.npz"), state_traj=st, action_traj=ac,
+                            ticks=self.ticks.cpu().numpy(), failed=self.failed.cpu().numpy(),
+                            track_id=np.zeros(self.B, np.int32) if self.track_id is None else self.track_id.cpu().numpy())
+        cfg = self.config
+        with open(os.path.join(data_dir, f"{name}_config.yaml"), "w") as f:
+            yaml.safe_dump(cfg.to_dict() if hasattr(cfg, "to_dict") else dict(cfg), f)
+
+    @staticmethod
+    def load(data_dir, name="batched"):
+        z = np.load(os.path.join(data_dir, f"{name}_batched.npz"))
+        return {k: z[k] for k in z.files}, load_config(os.path.join(data_dir, f"{name}_config.yaml"))
+
+    def export_vehicle(self, b, data_dir, name="cascaded"):
+        """Vehicle b in the reference's own run format (racing.py:441-450): `{name}_state_traj.npy`, `_action_traj.npy`,
+        `_elapsed.npy`, `_config.yaml` (and `_preds.npy` = rel2glob of the states, one row per tick), so that the
+        reference's replay / summarize tooling reads it."""
+        os.makedirs(data_dir, exist_ok=True)
+        st, ac = self._trajectories()
+        T = int(self.ticks[b])
+        s, a = st[:T + 1, b], ac[:T + 1, b]
+        np.save(os.path.join(data_dir, f"{name}_state_traj.npy"), s)
+        np.save(os.path.join(data_dir, f"{name}_action_traj.npy"), a)
+        np.save(os.path.join(data_dir, f"{name}_elapsed.npy"), np.zeros(T))
+        e = self.engine
+        xy = e.rel2glob(e.tensor(s[:-1, 4]), e.tensor(s[:-1, 5]), e.tensor(s[:-1, 6])).cpu().numpy()
+        np.save(os.path.join(data_dir, f"{name}_preds.npy"), xy[:, None, :])
+        cfg = self.config
+        with open(os.path.join(data_dir, f"{name}_config.yaml"), "w") as f:
+            yaml.safe_dump(cfg.to_dict() if hasattr(cfg, "to_dict") else dict(cfg), f)
+
+    def summary(self):
+        """racing.py:92-106 for every vehicle at once: arrays [B] of lap time, average speed, mean |Fx|, std Fx, mean
+        squared lateral deviation (over each vehicle's own ticks), plus the fleet aggregates."""
+        st, ac = self._trajectories()
+        T = self.ticks.cpu().numpy()
+        k = np.arange(st.shape[0])[:, None]
+        ms = (k <= T[None]).astype(float)                       # states 0..T[b]
+        ma = ((k >= 1) & (k <= T[None])).astype(float)          # actions 1..T[b] (row 0 is the placeholder)
+        ns, na = ms.sum(0), np.maximum(ma.sum(0), 1.0)
+        fx = ac[:, :, 0]
+        # the reference averages |Fx| and std over the whole action array including the zero placeholder row
+        nfull = na + 1.0
+        mean_fx = (ma * np.abs(fx)).sum(0) / nfull
+        mfx = (ma * fx).sum(0) / nfull
+        out = {"laptime": st[np.minimum(T, st.shape[0] - 1), np.arange(self.B), 7], "ticks": T,
+               "finished": ~self.failed.cpu().numpy() & (self.x[:, 4] > self.lengths - 0.1).cpu().numpy(),
+               "average_speed": (ms * st[:, :, 0]).sum(0) / ns, "mean_abs_Fx": mean_fx,
+               "std_Fx": np.sqrt(np.maximum(((ma * fx ** 2).sum(0) + 0.0) / nfull - mfx ** 2, 0.0)),
+               "mean_squared_ey": (ms * st[:, :, 5] ** 2).sum(0) / ns}
+        fin = out["finished"]
+        out["fleet"] = {"vehicles": int(self.B), "finished": int(fin.sum()), "failed": int(self.failed.sum()),
+                        "median_laptime": float(np.median(out["laptime"][fin])) if fin.any() else float("nan"),
+                        "total_solves": int(self.total_solves), "retries": dict(self.controller.retries)}
+        return out
+
+    def summarize(self):
+        s = self.summary()
+        print(f"vehicles {s['fleet']['vehicles']}: finished {s['fleet']['finished']}, failed {s['fleet']['failed']}")
+        print(f"Laptime: median {s['fleet']['median_laptime']}  min {np.min(s['laptime'])}  max {np.max(s['laptime'])}")
+        print(f"Average speed: {np.mean(s['average_speed'])}")
+        print(f"Mean Fx: {np.mean(s['mean_abs_Fx'])}")
+        print(f"Mean squared error: {np.mean(s['mean_squared_ey'])}")
