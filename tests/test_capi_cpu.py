@@ -42,3 +42,18 @@ def test_product_does_not_import_oracle():
                 if re.search(r"^\s*(from|import)\s+oracle\b", txt, re.M):
                     bad.append(f)
     assert not bad, bad
+
+
+def test_handwritten_adjoints_match_hyperdual_templates(tmp_path):
+    """vc_adj.cuh (forward-over-reverse stage Lagrangian, what k_eval_st runs) compiled for the host against the
+    hyper-dual templates of vc_model.cuh / vc_nlp.cuh: values exact, gradient and Hessian columns to 1e-10."""
+    import shutil
+    import subprocess
+    cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else shutil.which("g++")
+    exe = str(tmp_path / "adj_check")
+    r = subprocess.run([cxx, "-O1", "-std=c++17", "-x", "c++", os.path.join(ROOT, "tests", "host", "adj_check.cpp"), "-o", exe],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-2000:]
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout[-2000:]
+    assert "cases 600" in r.stdout

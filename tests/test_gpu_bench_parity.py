@@ -112,3 +112,28 @@ def test_block_wide_kernels_equal_warp_kernels_bit_for_bit():
         res.append((X.clone(), U.clone(), out["obj"].clone(), out["iters"].clone(), out["status"].clone()))
     for a, b in zip(*res):
         assert torch.equal(a, b)
+
+
+def test_command_host_equals_device_path_and_oracle():
+    """vc_nmpc_command_host (the reference-facing call with HOST buffers: horizon parameters, solve and all copies inside
+    one call -- the call bench.py's `e2e` times) against the device-pointer path on the same instances (bit for bit: the
+    same kernels run) and against the oracle's answers."""
+    f = _fx("c3")
+    eng, cfg = _engine("c3")
+    n = len(f["x0"])
+    x0, X, U = eng.tensor(f["x0"]), eng.tensor(f["Xw"]), eng.tensor(f["Uw"])
+    ob = eng.tensor(f["obst"])
+    ds, kap = eng.horizon_params(x0, X)
+    dev = eng.solve(x0, kap, ds, X, U, obstacles=ob)
+    hX, hU = np.ascontiguousarray(f["Xw"]).copy(), np.ascontiguousarray(f["Uw"]).copy()
+    host = eng.command_host(np.ascontiguousarray(f["x0"]), hX, hU, np.ascontiguousarray(f["obst"]))
+    assert (host["status"] == 0).all()
+    assert np.array_equal(host["iters"], dev["iters"].cpu().numpy())
+    assert np.array_equal(hU, U.cpu().numpy()) and np.array_equal(hX, X.cpu().numpy())
+    assert np.array_equal(host["obj"], dev["obj"].cpu().numpy())
+    assert _rel(hU, f["U"]).max() < TOL and _rel(host["obj"], f["obj"]).max() < TOL
+    # a second call on a smaller batch reuses the handle's staging buffers
+    m = n // 2
+    hX2, hU2 = np.ascontiguousarray(f["Xw"][:m]).copy(), np.ascontiguousarray(f["Uw"][:m]).copy()
+    h2 = eng.command_host(np.ascontiguousarray(f["x0"][:m]), hX2, hU2, np.ascontiguousarray(f["obst"][:m]))
+    assert np.array_equal(hU2, hU[:m]) and np.array_equal(h2["iters"], host["iters"][:m])
