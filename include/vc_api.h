@@ -139,6 +139,20 @@ int vc_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_kappa
                   const double* d_obst, int n_obs, double* d_X, double* d_U, double* d_obj, int* d_status,
                   int* d_iters, double* d_kkt);
 
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (a tight serving loop, a harness that forbids allocation).  Same arguments, kernels and results as vc_nmpc_solve, but the
+ * call allocates NOTHING: the solver workspace and the lists of unfinished instances live in a file-scope
+ * `static __device__` array of VC_STATIC_SCRATCH_BYTES (16 MiB) inside the library, which every GPU that loads the library
+ * holds until the process exits.  Limit: B * ((596 * H + 112) * 8 + 8) + 264 <= VC_STATIC_SCRATCH_BYTES with H = N + M, i.e.
+ * at most 63 instances at H = 55 (cascaded 20 + 35), 99 at H = 35, 70 at H = 50; a larger request is rejected with an error
+ * (vc_last_error) and nothing is launched.  All handles and all calls on one GPU share the array: two calls that overlap on
+ * the GPU (different streams or handles) race -- serialise them.  The array keeps the previous call's contents; the call
+ * re-initialises every record it uses.  Like vc_nmpc_solve it reads one int back per pass (it is not capturable). */
+#define VC_STATIC_SCRATCH_BYTES (16u << 20)
+int vc_nmpc_solve_static(vc_handle* h, int B, const double* d_x0, const double* d_kappa, const double* d_ds,
+                         const double* d_obst, int n_obs, double* d_X, double* d_U, double* d_obj, int* d_status,
+                         int* d_iters, double* d_kkt);
+
 /* Objective / constraint residual of a given trajectory (no solve): diagnostics + parity tests.
  * d_out[B,3] = objective, max equality violation, min inequality margin. */
 int vc_nmpc_eval(vc_handle* h, int B, const double* d_x0, const double* d_kappa, const double* d_ds,

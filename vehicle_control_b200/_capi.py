@@ -54,6 +54,7 @@ EXPORTS = {
     "vc_plant_step_tracks": (C.c_int, [C.c_void_p, C.c_int, PD, PD, PD, D]),
     "vc_tyre_forces": (C.c_int, [C.c_void_p, C.c_int, PD, PD, PD]),
     "vc_nmpc_solve": (C.c_int, [C.c_void_p, C.c_int, PD, PD, PD, PD, C.c_int, PD, PD, PD, PD, PD, PD]),
+    "vc_nmpc_solve_static": (C.c_int, [C.c_void_p, C.c_int, PD, PD, PD, PD, C.c_int, PD, PD, PD, PD, PD, PD]),
     "vc_nmpc_eval": (C.c_int, [C.c_void_p, C.c_int, PD, PD, PD, PD, C.c_int, PD, PD, PD]),
     "vc_nmpc_solve_host": (C.c_int, [C.c_void_p, C.c_int, PD, PD, PD, PD, C.c_int, PD, PD, PD, PD, PD, PD]),
     "vc_nmpc_command_host": (C.c_int, [C.c_void_p, C.c_int, PD, PD, C.c_int, PD, PD, PD, PD, PD, PD]),

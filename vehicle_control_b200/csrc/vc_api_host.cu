@@ -14,6 +14,14 @@ int vc_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_kappa
     return launch_nmpc_solve(h, B, d_x0, d_kappa, d_ds, d_obst, n_obs, d_X, d_U, d_obj, d_status, d_iters, d_kkt);
 }
 
+int vc_nmpc_solve_static(vc_handle* h, int B, const double* d_x0, const double* d_kappa, const double* d_ds,
+                         const double* d_obst, int n_obs, double* d_X, double* d_U, double* d_obj, int* d_status,
+                         int* d_iters, double* d_kkt) {
+    if (!h) { set_error("vc_nmpc_solve_static: null handle"); return -1; }
+    if (B <= 0) return 0;
+    return launch_nmpc_solve_static(h, B, d_x0, d_kappa, d_ds, d_obst, n_obs, d_X, d_U, d_obj, d_status, d_iters, d_kkt);
+}
+
 int vc_nmpc_eval(vc_handle* h, int B, const double* d_x0, const double* d_kappa, const double* d_ds,
                  const double* d_obst, int n_obs, const double* d_X, const double* d_U, double* d_out) {
     if (!h) { set_error("vc_nmpc_eval: null handle"); return -1; }

@@ -50,6 +50,9 @@ int check_cuda(cudaError_t e, const char* what);
 int launch_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_kappa, const double* d_ds,
                       const double* d_obst, int n_obs, double* d_X, double* d_U, double* d_obj, int* d_status,
                       int* d_iters, double* d_kkt);
+int launch_nmpc_solve_static(vc_handle* h, int B, const double* d_x0, const double* d_kappa, const double* d_ds,
+                             const double* d_obst, int n_obs, double* d_X, double* d_U, double* d_obj, int* d_status,
+                             int* d_iters, double* d_kkt);
 int launch_nmpc_eval(vc_handle* h, int B, const double* d_x0, const double* d_kappa, const double* d_ds,
                      const double* d_obst, int n_obs, const double* d_X, const double* d_U, double* d_out);
 int debug_read(vc_handle* h, int b, int array, double* h_out, int n);

@@ -15,6 +15,7 @@
 #include <cstdio>
 #include <cstring>
 #include <cstdlib>
+#include <mutex>
 #include <vector>
 #include "vc_handle.h"
 #include "vc_adj.cuh"
@@ -1946,6 +1947,105 @@ int launch_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_k
         }
     }
     return check_cuda(cudaGetLastError(), "nmpc solve");
+}
+
+
+// ---- vc_nmpc_solve_static: the same solve with NO allocation (include/vc_api.h) -------------------------------------------
+// Callers that may not call cudaMalloc (a tight serving loop, a harness that forbids it) get the solver workspace and the
+// two active lists from this file-scope array instead of the handle's cudaMalloc'ed slab.  Every GPU that loads the library
+// holds the 16 MiB until exit; every call shares them (calls that overlap on one GPU race), and they keep the last call's
+// contents: k_prepare re-initialises every instance record it uses and the pass loop clears the list counters.
+constexpr size_t STATIC_SCRATCH_BYTES = (size_t)VC_STATIC_SCRATCH_BYTES;
+static __device__ __align__(256) unsigned char g_static_scratch[STATIC_SCRATCH_BYTES];
+constexpr int STATIC_MAX_DEVICES = 64;
+static unsigned char* g_static_scratch_addr[STATIC_MAX_DEVICES] = {};   // device address of the array, per device
+static std::mutex g_static_mutex;
+
+// In host code `g_static_scratch` is only a stand-in for the symbol: the device address comes from cudaGetSymbolAddress,
+// once per device, with that device current.
+static int static_scratch_address(int device, unsigned char** out) {
+    if (device < 0 || device >= STATIC_MAX_DEVICES) { set_error("vc_nmpc_solve_static: device index out of range"); return -1; }
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    if (!g_static_scratch_addr[device]) {
+        int rc = check_cuda(cudaSetDevice(device), "cudaSetDevice(static scratch)");
+        if (rc) return rc;
+        void* ptr = nullptr;
+        rc = check_cuda(cudaGetSymbolAddress(&ptr, g_static_scratch), "cudaGetSymbolAddress(static scratch)");
+        if (rc) return rc;
+        if (!ptr) { set_error("vc_nmpc_solve_static: null symbol address"); return -1; }
+        g_static_scratch_addr[device] = (unsigned char*)ptr;
+    }
+    *out = g_static_scratch_addr[device];
+    return 0;
+}
+
+int launch_nmpc_solve_static(vc_handle* h, int B, const double* d_x0, const double* d_kappa, const double* d_ds,
+                             const double* d_obst, int n_obs, double* d_X, double* d_U, double* d_obj, int* d_status,
+                             int* d_iters, double* d_kkt) {
+    Prob pr;
+    int rc = fill_prob(h, pr, B, d_x0, d_kappa, d_ds, d_obst, n_obs);
+    if (rc) return rc;
+    if (!d_X || !d_U) { set_error("nmpc: null X/U pointer"); return -1; }
+    pr.X = d_X; pr.U = d_U; pr.obj = d_obj; pr.kkt = d_kkt; pr.status = d_status; pr.iters = d_iters;
+    Ws ws;
+    ws.H = pr.H;
+    ws.stride = (size_t)WS_PER_STAGE * pr.H + NSCAL;
+    const size_t ws_bytes = (ws.stride * sizeof(double) * (size_t)B + 255) & ~(size_t)255;
+    const size_t list_bytes = sizeof(int) * (2 * (size_t)B + 2);
+    if (ws_bytes + list_bytes > STATIC_SCRATCH_BYTES) {
+        char msg[256];
+        snprintf(msg, sizeof(msg), "vc_nmpc_solve_static: B = %d instances at horizon %d need %zu bytes of scratch, the static "
+                 "array holds %zu (at most %zu instances at this horizon); use vc_nmpc_solve", B, pr.H, ws_bytes + list_bytes,
+                 STATIC_SCRATCH_BYTES, (STATIC_SCRATCH_BYTES - 256 - 8) / (ws.stride * sizeof(double) + 2 * sizeof(int)));
+        set_error(msg);
+        return -1;
+    }
+    unsigned char* scratch = nullptr;
+    rc = static_scratch_address(h->device, &scratch);
+    if (rc) return rc;
+    cudaSetDevice(h->device);
+    ws.base = (double*)scratch;
+    int* act = (int*)(scratch + ws_bytes);
+    int* counts[2] = {act, act + 1};
+    int* lists[2] = {act + 2, act + 2 + B};
+    cudaStream_t st = h->stream;
+    k_prepare<<<(B * pr.H + 127) / 128, 128, 0, st>>>(pr, ws, lists[0], counts[0]);
+    h->launches++;
+    int cur = 0, n_act = B, pass = 0;
+    const int max_pass = h->cfg.max_iter + h->cfg.max_iter / 8 + 32;
+    const int wide_max = h->cfg.wide_max;
+    for (; pass < max_pass; ++pass) {
+        const long long t_st = (long long)n_act * pr.N * EVAL_ST_LANES, t_pm = (long long)n_act * pr.M * 15;
+        pr.act_list = lists[cur]; pr.act_count = counts[cur];
+        k_eval_st<<<(unsigned)((t_st + 127) / 128), 128, 0, st>>>(pr, ws);
+        if (pr.M > 0) k_eval_pm<<<(unsigned)((t_pm + 127) / 128), 128, 0, st>>>(pr, ws);
+        cudaMemsetAsync(counts[1 - cur], 0, sizeof(int), st);
+        if (n_act <= wide_max) {
+            k_step_a_wide<<<n_act, WIDE_NT, 0, st>>>(pr, ws);
+            k_step_b_wide<<<n_act, 32 * LS_TRIALS, 0, st>>>(pr, ws, lists[1 - cur], counts[1 - cur]);
+        } else {
+            k_step_a<<<(n_act + STEP_WARPS - 1) / STEP_WARPS, 32 * STEP_WARPS, 0, st>>>(pr, ws);
+            k_step_b<<<(n_act + STEP_WARPS - 1) / STEP_WARPS, 32 * STEP_WARPS, 0, st>>>(pr, ws, lists[1 - cur], counts[1 - cur]);
+        }
+        k_update<<<(unsigned)(((long long)n_act * pr.H * 32 + 127) / 128), 128, 0, st>>>(pr, ws);
+        cur = 1 - cur;
+        h->launches += pr.M > 0 ? 5 : 4;
+        if (pass >= 3) {   // survivors of this pass, read into a stack variable (no pinned buffer to allocate)
+            int left = 0;
+            cudaMemcpyAsync(&left, counts[cur], sizeof(int), cudaMemcpyDeviceToHost, st);
+            rc = check_cuda(cudaStreamSynchronize(st), "nmpc iteration (static scratch)");
+            if (rc) return rc;
+            n_act = left;
+            if (n_act == 0) break;
+        }
+    }
+    if (n_act > 0) {
+        pr.act_list = lists[cur]; pr.act_count = counts[cur];
+        k_finalize_survivors<<<(n_act * 32 + 127) / 128, 128, 0, st>>>(pr, ws);
+        h->launches++;
+    }
+    h->last_passes = pass < max_pass ? pass + 1 : max_pass;
+    return check_cuda(cudaGetLastError(), "nmpc solve (static scratch)");
 }
 
 

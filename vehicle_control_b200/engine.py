@@ -223,6 +223,20 @@ class Engine:
                                      self._p(out["iters"], dtype=torch.int32), self._p(out["kkt"])), "vc_nmpc_solve")
         return out
 
+    def solve_static(self, x0, kappa, ds, X, U, out, obstacles=None):
+        """`solve` through vc_nmpc_solve_static: nothing is allocated inside the call (the solver's scratch is a static
+        16 MiB device array of the library, at most 63 instances at H = 55), so `out` (obj, status, iters, kkt) must be
+        given.  No counterpart in the reference; calls that overlap on one GPU race (include/vc_api.h)."""
+        B, H = x0.shape[0], self.H
+        n_obs = 0 if obstacles is None else obstacles.shape[1]
+        check(self.lib.vc_nmpc_solve_static(self._h, B, self._p(x0, (B, 8)), self._p(kappa, (B, H)), self._p(ds, (B, H)),
+                                            self._p(obstacles, (B, n_obs, 3)) if n_obs else None, n_obs,
+                                            self._p(X, (B, 8, H)), self._p(U, (B, 2, H)), self._p(out["obj"]),
+                                            self._p(out["status"], dtype=torch.int32),
+                                            self._p(out["iters"], dtype=torch.int32), self._p(out["kkt"])),
+              "vc_nmpc_solve_static")
+        return out
+
     def evaluate(self, x0, kappa, ds, X, U, obstacles=None):
         """[B,3] objective, max equality violation, min inequality margin of a given trajectory."""
         B, H = x0.shape[0], self.H
