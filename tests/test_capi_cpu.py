@@ -57,3 +57,19 @@ def test_handwritten_adjoints_match_hyperdual_templates(tmp_path):
     r = subprocess.run([exe], capture_output=True, text=True)
     assert r.returncode == 0, r.stdout[-2000:]
     assert "cases 600" in r.stdout
+
+
+def test_handderived_rk4_jacobian_matches_dual_numbers(tmp_path):
+    """vc_jac.cuh (hand-derived Jacobian of the spatial SingleTrack right-hand side chained through RK4, what
+    k_rollout_st_jac_an runs) compiled for the host against the forward-mode dual numbers of vc_ad.cuh / vc_model.cuh
+    (dynamic_car.py:78-191, integrators.py:26-37): values to 1e-13, all 80 entries of [A|B] to 1e-11, both Fiala branches."""
+    import shutil
+    import subprocess
+    cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else shutil.which("g++")
+    exe = str(tmp_path / "jac_check")
+    r = subprocess.run([cxx, "-O1", "-std=c++17", "-x", "c++", os.path.join(ROOT, "tests", "host", "jac_check.cpp"), "-o", exe],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-2000:]
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout[-2000:]
+    assert "cases 2000" in r.stdout

@@ -3,9 +3,10 @@
 // All arithmetic fp64; none of it is a dense contraction, so no tensor cores.
 #include "vc_handle.h"
 #include "vc_model.cuh"
+#include "vc_jac.cuh"
 #include <cstdlib>
 #ifndef VC_JAC_K_DEFAULT
-#define VC_JAC_K_DEFAULT 2
+#define VC_JAC_K_DEFAULT 0
 #endif
 
 namespace vc {
@@ -134,6 +135,118 @@ k_rollout_st_jac_k(Params p, int B, int N, const double* __restrict__ x0, const 
             double* out = AB + bn * 80;
 #pragma unroll
             for (int q = 0; q < 80 / L; ++q) out[q * L + j] = tile[g][q * L + j];
+        }
+        __syncwarp();
+    }
+}
+
+// K1d: the same outputs from the hand-derived Jacobian of the right-hand side (vc_jac.cuh) chained through the four RK4
+// stages.  One thread per trajectory: the 39 non-zero partials of one right-hand-side evaluation live in registers, the
+// sensitivity D = d(active states)/d(x0 active, u) (6 x 8) and the weighted sum of the stage Jacobians (7 x 8) live in
+// shared memory, element-major with the thread index fastest (stride KA_LD: conflict-free for the owner thread and for
+// the warp-cooperative read-out).  After the fourth stage the warp writes each trajectory's 8x10 block as one 640-byte
+// run.  About a third of the arithmetic of the dual-number kernels: no value or transcendental is evaluated twice.
+#define KA_TPB 64
+constexpr int KA_LD = KA_TPB + 1;
+constexpr int KA_ROWS = 48 + 56 + 1;   // D, acc, h/6
+__global__ void __launch_bounds__(KA_TPB)
+k_rollout_st_jac_an(Params p, int B, int N, const double* __restrict__ x0, const double* __restrict__ U,
+                    const double* __restrict__ kappa, const double* __restrict__ ds, double* __restrict__ X,
+                    double* __restrict__ AB) {
+    extern __shared__ double ka_sm[];
+    const int tid = threadIdx.x, lane = tid & 31, wbase = tid & ~31;
+    double* sD = ka_sm + tid;                       // element e of this thread: sD[e * KA_LD]
+    double* sA = ka_sm + 48 * KA_LD + tid;
+    double* sH = ka_sm + 104 * KA_LD;
+    const int b = blockIdx.x * KA_TPB + tid;
+    const bool live = b < B;
+    const int bb = live ? b : B - 1;
+    // entries of the 8x10 output block written by this lane: o = lane + 32 q
+    int o_src[3];
+    double o_unit[3];
+#pragma unroll
+    for (int q = 0; q < 3; ++q) {
+        const int o = lane + 32 * q, row = o / 10, col = o - row * 10;
+        const int i = row < 4 ? row : (row == IS ? -1 : row - 1);                    // Ux Uy r delta | ey epsi t -> 0..6
+        const int c = col < 4 ? col : ((col == IS || col == IT) ? -1 : (col < IT ? col - 1 : col - 2));   // -> 0..7
+        o_src[q] = (o < 80 && i >= 0 && c >= 0) ? c * 7 + i : -1;
+        o_unit[q] = row == col ? 1.0 : 0.0;
+    }
+    double x[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) x[i] = x0[(size_t)bb * 8 + i];
+    double* Xb = X + (size_t)bb * (N + 1) * 8;
+    if (live) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) Xb[i] = x[i];
+    }
+    const size_t blk0 = (size_t)blockIdx.x * KA_TPB + wbase;   // first trajectory of this warp
+    for (int n = 0; n < N; ++n) {
+        const size_t bn = (size_t)bb * N + n;
+        double u[2] = {U[bn * 2], U[bn * 2 + 1]};
+        const double kap = kappa[bn], h = ds[bn];
+        double xs[8], f[8], facc[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) xs[i] = x[i];
+#pragma unroll 1
+        for (int s = 0; s < 4; ++s) {
+            StRhsJac J;
+            st_rhs_spatial_jac(p, xs, u, kap, f, J);
+            const double wgt = (s == 0 || s == 3) ? 1.0 : 2.0;
+            const double cs = s == 2 ? h : 0.5 * h;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                if (s == 0) facc[i] = f[i]; else facc[i] = facc[i] + wgt * f[i];
+                xs[i] = x[i] + cs * f[i];
+            }
+            if (s == 0) {   // D = [I | 0]: K = J
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    double d[6], k[7];
+#pragma unroll
+                    for (int i = 0; i < 6; ++i) d[i] = c == i ? 1.0 : 0.0;
+                    st_jac_unitcol(J, c, k);
+#pragma unroll
+                    for (int i = 0; i < 7; ++i) sA[(c * 7 + i) * KA_LD] = k[i];
+#pragma unroll
+                    for (int i = 0; i < 6; ++i) sD[(c * 6 + i) * KA_LD] = d[i] + cs * k[i];
+                }
+            } else {
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    double d[6], k[7];
+#pragma unroll
+                    for (int i = 0; i < 6; ++i) d[i] = sD[(c * 6 + i) * KA_LD];
+                    st_jac_col(J, d, c < 6 ? 0 : c - 5, k);
+#pragma unroll
+                    for (int i = 0; i < 7; ++i) sA[(c * 7 + i) * KA_LD] += wgt * k[i];
+                    if (s < 3) {
+#pragma unroll
+                        for (int i = 0; i < 6; ++i) sD[(c * 6 + i) * KA_LD] = (c == i ? 1.0 : 0.0) + cs * k[i];
+                    }
+                }
+            }
+        }
+        const double h6 = h * (1.0 / 6.0);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) x[i] = x[i] + h6 * facc[i];
+        if (live) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) Xb[(n + 1) * 8 + i] = x[i];
+        }
+        sH[tid] = h6;
+        __syncwarp();
+        for (int t = 0; t < 32; ++t) {
+            const size_t bt = blk0 + t;
+            if (bt >= (size_t)B) break;
+            const double ht = sH[wbase + t];
+            const double* a = ka_sm + 48 * KA_LD + wbase + t;
+            double* out = AB + (bt * N + n) * 80;
+#pragma unroll
+            for (int q = 0; q < 3; ++q) {
+                const int o = lane + 32 * q;
+                if (o < 80) out[o] = o_src[q] < 0 ? o_unit[q] : o_unit[q] + ht * a[o_src[q] * KA_LD];
+            }
         }
         __syncwarp();
     }
@@ -478,7 +591,13 @@ int vc_rollout_st(vc_handle* h, int B, int N, const double* d_x0, const double* 
     if (B <= 0) return 0;
     if (d_AB) {
         static const int jac_k = getenv("VC_JAC_K") ? atoi(getenv("VC_JAC_K")) : VC_JAC_K_DEFAULT;   // Jacobian columns per lane
-        if (jac_k == 2) {
+        if (jac_k == 0) {   // hand-derived Jacobian (default)
+            constexpr size_t smem = sizeof(double) * KA_ROWS * KA_LD;
+            int rc = check_cuda(cudaFuncSetAttribute(k_rollout_st_jac_an, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
+                                "cudaFuncSetAttribute(k_rollout_st_jac_an)");
+            if (rc) return rc;
+            k_rollout_st_jac_an<<<(B + KA_TPB - 1) / KA_TPB, KA_TPB, smem, h->stream>>>(h->params, B, N, d_x0, d_U, d_kappa, d_ds, d_X, d_AB);
+        } else if (jac_k == 2) {
             constexpr int G = K1_TPB / 4;
             k_rollout_st_jac_k<2><<<(B + G - 1) / G, K1_TPB, 0, h->stream>>>(h->params, B, N, d_x0, d_U, d_kappa, d_ds, d_X, d_AB);
         } else if (jac_k == 4) {
