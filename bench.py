@@ -43,6 +43,8 @@ def parse():
     ap.add_argument("--cpu-instances", type=int, default=0, help="instances per step of the CPU arm (0 = default sample)")
     ap.add_argument("--scaling", default="strong", choices=["strong", "weak"],
                     help="strong: the configuration's batch is split over the GPUs; weak: every GPU gets the whole batch")
+    ap.add_argument("--in-flight", type=int, default=3, dest="in_flight",
+                    help="C3: batches in flight per GPU (lanes: handle + stream + workspace + host thread each); 1 = one batch at a time")
     ap.add_argument("--lap-cache", default=None, help="npz file to save/load the untimed warm-start lap (profiling runs)")
     ap.add_argument("--rollout-batch", type=int, default=0, help="trajectories of the C5 leg (0 = 1,048,576)")
     ap.add_argument("--no-secondary", action="store_true", help="skip the C5 block of the default line")

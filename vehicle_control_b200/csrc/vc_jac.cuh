@@ -13,20 +13,19 @@
 
 namespace vc {
 
-// d f_spatial / d v, row by row, non-zero entries only
+// d f_spatial / d v in factored form.  With f_i = g_i / s_dot:  d f_i = g_i,v / s_dot - f_i (s_dot,v / s_dot), so every row
+// is its "temporal" part (sparse) minus f_i times ONE common row sv = s_dot,v / s_dot (columns Ux Uy ey epsi).
 struct StRhsJac {
-    double ux[7], uy[7], rr[7];   // rows Ux', Uy', r'   : columns Ux Uy r delta ey epsi Fx
-    double dl[5];                 // row delta'          : columns Ux Uy ey epsi w
-    double ey[4];                 // row ey'             : columns Ux Uy ey epsi
-    double ep[5];                 // row epsi'           : columns Ux Uy r ey epsi
-    double tt[4];                 // row t'              : columns Ux Uy ey epsi
+    double g[3][5];        // rows Ux', Uy', r': temporal partials / s_dot, columns Ux Uy r delta Fx
+    double sv[4];          // s_dot,v / s_dot, columns Ux Uy ey epsi
+    double fU, fV, fR, fD, fE, ris, is;   // f of rows Ux Uy r delta ey, r / s_dot, 1 / s_dot
+    double eU, eV, eP;     // row ey': temporal partials / s_dot, columns Ux Uy epsi
 };
 
 // partial derivatives of the modified Fiala force (same branches as fiala() in vc_model.cuh)
-VC_HD void fiala_partials(double C, double eps, double ta, double fymax, double& fy, double& d_ta, double& d_fm) {
-    const double tmod = 3.0 * fymax * eps / C;
+VC_HD void fiala_partials(double C, double eps, double ta, double fymax, double inv, double& fy, double& d_ta, double& d_fm) {
+    const double tmod = 3.0 * fymax * eps / C;   // (C is a parameter: the quotient is formed as in fiala())
     if (fabs(ta) <= tmod) {
-        const double inv = 1.0 / fymax;
         const double at = fabs(ta);
         fy = -C * ta + (C * C / 3.0) * (at * ta) * inv - (C * C * C / 27.0) * (ta * ta * ta) * (inv * inv);
         d_ta = (2.0 * C * C / 3.0) * (at * inv) - (C * C * C / 9.0) * ((ta * ta) * (inv * inv)) - C;
@@ -40,20 +39,26 @@ VC_HD void fiala_partials(double C, double eps, double ta, double fymax, double&
     }
 }
 
-// f = d x / d s (values in the operation order of st_rhs<true, double>) and its Jacobian
-VC_HD void st_rhs_spatial_jac(const Params& p, const double* x, const double* u, double kappa, double* f, StRhsJac& J) {
-    const double Ux = x[IUX], Uy = x[IUY], r = x[IR], delta = x[IDELTA], ey = x[IEY], epsi = x[IEPSI];
-    const double Fx = u[0], w = u[1];
-    // ---- tyres (vc_model.cuh: force_split, normal_loads, tyres)
+// what depends on the control Fx only (the same for the four RK4 stages of a step): drive/brake split and its derivative
+struct StCtl { double fxf, fxr, fxf_F, fxr_F, shift; };
+VC_HD void st_ctl(const Params& p, double Fx, StCtl& c) {
     const double th = tanh(2.0 * (Fx / 1000.0 + 0.5));
     const double dth = (1.0 - th * th) * (2.0 / 1000.0);
     const double cf1 = (p.Xdf - p.Xbf) / 2, cr1 = (p.Xdr - p.Xbr) / 2;
     const double Xf = cf1 * th + (p.Xdf + p.Xbf) / 2;
     const double Xr = cr1 * th + (p.Xdr + p.Xbr) / 2;
-    const double fxf = Fx * Xf, fxr = Fx * Xr;
-    const double fxf_F = Xf + Fx * (cf1 * dth), fxr_F = Xr + Fx * (cr1 * dth);
+    c.fxf = Fx * Xf; c.fxr = Fx * Xr;
+    c.fxf_F = Xf + Fx * (cf1 * dth); c.fxr_F = Xr + Fx * (cr1 * dth);
+    c.shift = (p.h / p.l) * Fx;
+}
+
+// f = d x / d s (the operations of st_rhs<true, double>; divisions by the constants m, Izz are multiplications by their
+// reciprocals) and its Jacobian
+VC_HD void st_rhs_spatial_jac(const Params& p, const StCtl& ct, const double* x, double w, double kappa, double* f, StRhsJac& J) {
+    const double Ux = x[IUX], Uy = x[IUY], r = x[IR], delta = x[IDELTA], ey = x[IEY], epsi = x[IEPSI];
+    // ---- tyres (vc_model.cuh: force_split, normal_loads, tyres)
+    const double fxf = ct.fxf, fxr = ct.fxr, fxf_F = ct.fxf_F, fxr_F = ct.fxr_F, shift = ct.shift;
     const double base = p.g_eff + p.Av2 * (Ux * Ux);
-    const double shift = (p.h / p.l) * Fx;
     const double fzf = (p.b / p.l) * p.m * base - shift;
     const double fzr = (p.a / p.l) * p.m * base + shift;
     const double base_U = 2.0 * p.Av2 * Ux;
@@ -79,8 +84,8 @@ VC_HD void st_rhs_spatial_jac(const Params& p, const double* x, const double* u,
     const double tan_f = (zf * cd - sd) * iden;
     const double tan_r = (Uy - p.b * r) * iux;
     double fyf, fyr, df_ta, df_fm, dr_ta, dr_fm;
-    fiala_partials(p.Caf, p.eps, tan_f, fmf, fyf, df_ta, df_fm);
-    fiala_partials(p.Car, p.eps, tan_r, fmr, fyr, dr_ta, dr_fm);
+    fiala_partials(p.Caf, p.eps, tan_f, fmf, ifmf, fyf, df_ta, df_fm);
+    fiala_partials(p.Car, p.eps, tan_r, fmr, ifmr, fyr, dr_ta, dr_fm);
     // d tan_f / d zf = 1 / den^2 ; d tan_f / d delta = -(1 + tan_f^2)
     const double tf_z = df_ta * (iden * iden);
     const double fyf_U = tf_z * (-zf * iux) + df_fm * fmf_U;
@@ -101,9 +106,10 @@ VC_HD void st_rhs_spatial_jac(const Params& p, const double* x, const double* u,
 #endif
     const double Fd = p.Frr + p.Cd * (Ux * Ux);
     const double lat = fyf * cd + fxf * sd;
-    const double Ux_dot = (fxf * cd - fyf * sd + fxr - Fd) / p.m + r * Uy;
-    const double Uy_dot = (lat + fyr) / p.m - r * Ux;
-    const double r_dot = (p.a * lat - p.b * fyr) / p.Izz;
+    const double im = 1.0 / p.m, iI = 1.0 / p.Izz;
+    const double Ux_dot = (fxf * cd - fyf * sd + fxr - Fd) * im + r * Uy;
+    const double Uy_dot = (lat + fyr) * im - r * Ux;
+    const double r_dot = (p.a * lat - p.b * fyr) * iI;
     const double q = 1.0 / (1.0 - kappa * ey);
     const double s_dot = (Ux * ce - Uy * se) * q;
     const double ey_dot = Ux * se + Uy * ce;
@@ -112,7 +118,6 @@ VC_HD void st_rhs_spatial_jac(const Params& p, const double* x, const double* u,
     f[IUX] = Ux_dot * is; f[IUY] = Uy_dot * is; f[IR] = r_dot * is; f[IDELTA] = w * is;
     f[IS] = 1.0; f[IEY] = ey_dot * is; f[IEPSI] = epsi_dot * is; f[IT] = is;
     // ---- temporal partials g_v of (Ux_dot, Uy_dot, r_dot), columns Ux Uy r delta Fx
-    const double im = 1.0 / p.m, iI = 1.0 / p.Izz;
     const double lat_U = fyf_U * cd, lat_V = fyf_V * cd, lat_r = fyf_r * cd;
     const double lat_d = fyf_d * cd - fyf * sd + fxf * cd;
     const double lat_F = fyf_F * cd + fxf_F * sd;
@@ -132,51 +137,43 @@ VC_HD void st_rhs_spatial_jac(const Params& p, const double* x, const double* u,
     const double c_d = (p.a * lat_d) * iI;
     const double c_F = (p.a * lat_F - p.b * fyr_F) * iI;
     // s_dot partials (columns Ux Uy ey epsi), pre-multiplied by 1/s_dot:  sv = s_v / s_dot
-    const double sU = (ce * q) * is, sV = (-se * q) * is, sE = kappa * q, sP = (-ey_dot * q) * is;
-    // ---- spatial rows: d(g / s_dot) = (g_v - f s_v) / s_dot = g_v is - f sv
-    const double fU = f[IUX], fV = f[IUY], fR = f[IR], fD = f[IDELTA], fE = f[IEY], fP = f[IEPSI];
-    J.ux[0] = a_U * is - fU * sU; J.ux[1] = a_V * is - fU * sV; J.ux[2] = a_r * is; J.ux[3] = a_d * is;
-    J.ux[4] = -fU * sE; J.ux[5] = -fU * sP; J.ux[6] = a_F * is;
-    J.uy[0] = b_U * is - fV * sU; J.uy[1] = b_V * is - fV * sV; J.uy[2] = b_r * is; J.uy[3] = b_d * is;
-    J.uy[4] = -fV * sE; J.uy[5] = -fV * sP; J.uy[6] = b_F * is;
-    J.rr[0] = c_U * is - fR * sU; J.rr[1] = c_V * is - fR * sV; J.rr[2] = c_r * is; J.rr[3] = c_d * is;
-    J.rr[4] = -fR * sE; J.rr[5] = -fR * sP; J.rr[6] = c_F * is;
-    J.dl[0] = -fD * sU; J.dl[1] = -fD * sV; J.dl[2] = -fD * sE; J.dl[3] = -fD * sP; J.dl[4] = is;
+    J.sv[0] = (ce * q) * is; J.sv[1] = (-se * q) * is; J.sv[2] = kappa * q; J.sv[3] = (-ey_dot * q) * is;
+    J.g[0][0] = a_U * is; J.g[0][1] = a_V * is; J.g[0][2] = a_r * is; J.g[0][3] = a_d * is; J.g[0][4] = a_F * is;
+    J.g[1][0] = b_U * is; J.g[1][1] = b_V * is; J.g[1][2] = b_r * is; J.g[1][3] = b_d * is; J.g[1][4] = b_F * is;
+    J.g[2][0] = c_U * is; J.g[2][1] = c_V * is; J.g[2][2] = c_r * is; J.g[2][3] = c_d * is; J.g[2][4] = c_F * is;
+    J.fU = f[IUX]; J.fV = f[IUY]; J.fR = f[IR]; J.fD = f[IDELTA]; J.fE = f[IEY]; J.ris = r * is; J.is = is;
     // ey_dot: /Ux = se, /Uy = ce, /epsi = Ux ce - Uy se
-    J.ey[0] = se * is - fE * sU; J.ey[1] = ce * is - fE * sV; J.ey[2] = -fE * sE; J.ey[3] = (Ux * ce - Uy * se) * is - fE * sP;
-    // epsi' = r / s_dot - kappa
-    const double ris = r * is;
-    J.ep[0] = -ris * sU; J.ep[1] = -ris * sV; J.ep[2] = is; J.ep[3] = -ris * sE; J.ep[4] = -ris * sP;
-    J.tt[0] = -is * sU; J.tt[1] = -is * sV; J.tt[2] = -is * sE; J.tt[3] = -is * sP;
-    (void)fP;
+    J.eU = se * is; J.eV = ce * is; J.eP = (Ux * ce - Uy * se) * is;
 }
 
 // K[:, c] = J * [D[:, c]; e_u(c)] for one column c of the sensitivity D = d(active states)/d v0 (rows Ux Uy r delta ey
 // epsi).  `d` = that column (6 values), cu = 0: state column, 1: column Fx, 2: column w.  k: rows Ux Uy r delta ey epsi t.
 VC_HD void st_jac_col(const StRhsJac& J, const double* d, int cu, double* k) {
-    k[0] = J.ux[0] * d[0] + J.ux[1] * d[1] + J.ux[2] * d[2] + J.ux[3] * d[3] + J.ux[4] * d[4] + J.ux[5] * d[5];
-    k[1] = J.uy[0] * d[0] + J.uy[1] * d[1] + J.uy[2] * d[2] + J.uy[3] * d[3] + J.uy[4] * d[4] + J.uy[5] * d[5];
-    k[2] = J.rr[0] * d[0] + J.rr[1] * d[1] + J.rr[2] * d[2] + J.rr[3] * d[3] + J.rr[4] * d[4] + J.rr[5] * d[5];
-    k[3] = J.dl[0] * d[0] + J.dl[1] * d[1] + J.dl[2] * d[4] + J.dl[3] * d[5];
-    k[4] = J.ey[0] * d[0] + J.ey[1] * d[1] + J.ey[2] * d[4] + J.ey[3] * d[5];
-    k[5] = J.ep[0] * d[0] + J.ep[1] * d[1] + J.ep[2] * d[2] + J.ep[3] * d[4] + J.ep[4] * d[5];
-    k[6] = J.tt[0] * d[0] + J.tt[1] * d[1] + J.tt[2] * d[4] + J.tt[3] * d[5];
-    if (cu == 1) { k[0] += J.ux[6]; k[1] += J.uy[6]; k[2] += J.rr[6]; }
-    if (cu == 2) k[3] += J.dl[4];
+    const double t = J.sv[0] * d[0] + J.sv[1] * d[1] + J.sv[2] * d[4] + J.sv[3] * d[5];
+    k[0] = J.g[0][0] * d[0] + J.g[0][1] * d[1] + J.g[0][2] * d[2] + J.g[0][3] * d[3] - J.fU * t;
+    k[1] = J.g[1][0] * d[0] + J.g[1][1] * d[1] + J.g[1][2] * d[2] + J.g[1][3] * d[3] - J.fV * t;
+    k[2] = J.g[2][0] * d[0] + J.g[2][1] * d[1] + J.g[2][2] * d[2] + J.g[2][3] * d[3] - J.fR * t;
+    k[3] = -J.fD * t;
+    k[4] = J.eU * d[0] + J.eV * d[1] + J.eP * d[5] - J.fE * t;
+    k[5] = J.is * d[2] - J.ris * t;
+    k[6] = -J.is * t;
+    if (cu == 1) { k[0] += J.g[0][4]; k[1] += J.g[1][4]; k[2] += J.g[2][4]; }
+    if (cu == 2) k[3] += J.is;
 }
 
 // column c of J itself (the product with D = [I | 0] of the first RK4 stage): c = Ux Uy r delta ey epsi Fx w
 VC_HD void st_jac_unitcol(const StRhsJac& J, int c, double* k) {
-    const int m4[8] = {0, 1, -1, -1, 2, 3, -1, -1};   // position of column c in the 4-entry rows (ey', t')
-    const int md[8] = {0, 1, -1, -1, 2, 3, -1, 4};    // ... in row delta'
-    const int me[8] = {0, 1, 2, -1, 3, 4, -1, -1};    // ... in row epsi'
-    k[0] = c < 7 ? J.ux[c] : 0.0;
-    k[1] = c < 7 ? J.uy[c] : 0.0;
-    k[2] = c < 7 ? J.rr[c] : 0.0;
-    k[3] = md[c] >= 0 ? J.dl[md[c]] : 0.0;
-    k[4] = m4[c] >= 0 ? J.ey[m4[c]] : 0.0;
-    k[5] = me[c] >= 0 ? J.ep[me[c]] : 0.0;
-    k[6] = m4[c] >= 0 ? J.tt[m4[c]] : 0.0;
+    const int ms[8] = {0, 1, -1, -1, 2, 3, -1, -1};   // position of column c in sv
+    const int mg[8] = {0, 1, 2, 3, -1, -1, 4, -1};    // ... in the rows g
+    const bool ht = ms[c] >= 0, hg = mg[c] >= 0;
+    const double t = ht ? J.sv[ms[c]] : 0.0;
+    k[0] = (hg ? J.g[0][mg[c]] : 0.0) - (ht ? J.fU * t : 0.0);
+    k[1] = (hg ? J.g[1][mg[c]] : 0.0) - (ht ? J.fV * t : 0.0);
+    k[2] = (hg ? J.g[2][mg[c]] : 0.0) - (ht ? J.fR * t : 0.0);
+    k[3] = (c == 7 ? J.is : 0.0) - (ht ? J.fD * t : 0.0);
+    k[4] = (c == 0 ? J.eU : (c == 1 ? J.eV : (c == 5 ? J.eP : 0.0))) - (ht ? J.fE * t : 0.0);
+    k[5] = (c == 2 ? J.is : 0.0) - (ht ? J.ris * t : 0.0);
+    k[6] = ht ? -J.is * t : 0.0;
 }
 
 // One RK4 step with its Jacobian, plain doubles, one caller per trajectory (host check and reference for the kernel).
@@ -189,9 +186,11 @@ VC_HD void st_rk4_jac(const Params& p, const double* x, const double* u, double 
     for (int c = 0; c < 8; ++c)
         for (int i = 0; i < 6; ++i) D[c][i] = (c == i) ? 1.0 : 0.0;
     for (int i = 0; i < 8; ++i) xs[i] = x[i];
+    StCtl ct;
+    st_ctl(p, u[0], ct);
     for (int s = 0; s < 4; ++s) {
         StRhsJac J;
-        st_rhs_spatial_jac(p, xs, u, kappa, f, J);
+        st_rhs_spatial_jac(p, ct, xs, u[1], kappa, f, J);
         const double wgt = (s == 0 || s == 3) ? 1.0 : 2.0;
         const double cs = s == 2 ? h : 0.5 * h;
         for (int i = 0; i < 8; ++i) {
@@ -200,7 +199,7 @@ VC_HD void st_rk4_jac(const Params& p, const double* x, const double* u, double 
         }
         for (int c = 0; c < 8; ++c) {
             double k[7];
-            st_jac_col(J, D[c], c < 6 ? 0 : c - 5, k);
+            if (s == 0) st_jac_unitcol(J, c, k); else st_jac_col(J, D[c], c < 6 ? 0 : c - 5, k);
             for (int i = 0; i < 7; ++i) acc[c][i] = s == 0 ? k[i] : acc[c][i] + wgt * k[i];
             for (int i = 0; i < 6; ++i) D[c][i] = ((c == i) ? 1.0 : 0.0) + cs * k[i];
         }

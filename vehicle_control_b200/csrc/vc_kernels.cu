@@ -148,7 +148,7 @@ k_rollout_st_jac_k(Params p, int B, int N, const double* __restrict__ x0, const 
 // run.  About a third of the arithmetic of the dual-number kernels: no value or transcendental is evaluated twice.
 #define KA_TPB 64
 constexpr int KA_LD = KA_TPB + 1;
-constexpr int KA_ROWS = 48 + 56 + 1;   // D, acc, h/6
+constexpr int KA_ROWS = 48 + 56;   // D, acc
 __global__ void __launch_bounds__(KA_TPB)
 k_rollout_st_jac_an(Params p, int B, int N, const double* __restrict__ x0, const double* __restrict__ U,
                     const double* __restrict__ kappa, const double* __restrict__ ds, double* __restrict__ X,
@@ -157,21 +157,9 @@ k_rollout_st_jac_an(Params p, int B, int N, const double* __restrict__ x0, const
     const int tid = threadIdx.x, lane = tid & 31, wbase = tid & ~31;
     double* sD = ka_sm + tid;                       // element e of this thread: sD[e * KA_LD]
     double* sA = ka_sm + 48 * KA_LD + tid;
-    double* sH = ka_sm + 104 * KA_LD;
     const int b = blockIdx.x * KA_TPB + tid;
     const bool live = b < B;
     const int bb = live ? b : B - 1;
-    // entries of the 8x10 output block written by this lane: o = lane + 32 q
-    int o_src[3];
-    double o_unit[3];
-#pragma unroll
-    for (int q = 0; q < 3; ++q) {
-        const int o = lane + 32 * q, row = o / 10, col = o - row * 10;
-        const int i = row < 4 ? row : (row == IS ? -1 : row - 1);                    // Ux Uy r delta | ey epsi t -> 0..6
-        const int c = col < 4 ? col : ((col == IS || col == IT) ? -1 : (col < IT ? col - 1 : col - 2));   // -> 0..7
-        o_src[q] = (o < 80 && i >= 0 && c >= 0) ? c * 7 + i : -1;
-        o_unit[q] = row == col ? 1.0 : 0.0;
-    }
     double x[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) x[i] = x0[(size_t)bb * 8 + i];
@@ -181,19 +169,25 @@ k_rollout_st_jac_an(Params p, int B, int N, const double* __restrict__ x0, const
         for (int i = 0; i < 8; ++i) Xb[i] = x[i];
     }
     const size_t blk0 = (size_t)blockIdx.x * KA_TPB + wbase;   // first trajectory of this warp
-    for (int n = 0; n < N; ++n) {
-        const size_t bn = (size_t)bb * N + n;
-        double u[2] = {U[bn * 2], U[bn * 2 + 1]};
-        const double kap = kappa[bn], h = ds[bn];
+    const int nt = (int)(blk0 >= (size_t)B ? 0 : ((size_t)B - blk0 < 32 ? (size_t)B - blk0 : 32));   // live trajectories of the warp
+    size_t bn = (size_t)bb * N;
+    double u0 = N > 0 ? U[bn * 2] : 0.0, u1 = N > 0 ? U[bn * 2 + 1] : 0.0, kap = N > 0 ? kappa[bn] : 0.0, h = N > 0 ? ds[bn] : 0.0;
+    for (int n = 0; n < N; ++n, ++bn) {
+        StCtl ct;
+        st_ctl(p, u0, ct);
+        const double w = u1, kp = kap, hh = h;
+        if (n + 1 < N) {   // next step's inputs travel while this step computes
+            u0 = U[(bn + 1) * 2]; u1 = U[(bn + 1) * 2 + 1]; kap = kappa[bn + 1]; h = ds[bn + 1];
+        }
         double xs[8], f[8], facc[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) xs[i] = x[i];
 #pragma unroll 1
         for (int s = 0; s < 4; ++s) {
             StRhsJac J;
-            st_rhs_spatial_jac(p, xs, u, kap, f, J);
+            st_rhs_spatial_jac(p, ct, xs, w, kp, f, J);
             const double wgt = (s == 0 || s == 3) ? 1.0 : 2.0;
-            const double cs = s == 2 ? h : 0.5 * h;
+            const double cs = s == 2 ? hh : 0.5 * hh;
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 if (s == 0) facc[i] = f[i]; else facc[i] = facc[i] + wgt * f[i];
@@ -202,14 +196,12 @@ k_rollout_st_jac_an(Params p, int B, int N, const double* __restrict__ x0, const
             if (s == 0) {   // D = [I | 0]: K = J
 #pragma unroll
                 for (int c = 0; c < 8; ++c) {
-                    double d[6], k[7];
-#pragma unroll
-                    for (int i = 0; i < 6; ++i) d[i] = c == i ? 1.0 : 0.0;
+                    double k[7];
                     st_jac_unitcol(J, c, k);
 #pragma unroll
-                    for (int i = 0; i < 7; ++i) sA[(c * 7 + i) * KA_LD] = k[i];
+                    for (int i = 0; i < 7; ++i) sA[(i * 8 + c) * KA_LD] = k[i];
 #pragma unroll
-                    for (int i = 0; i < 6; ++i) sD[(c * 6 + i) * KA_LD] = d[i] + cs * k[i];
+                    for (int i = 0; i < 6; ++i) sD[(c * 6 + i) * KA_LD] = (c == i ? 1.0 : 0.0) + cs * k[i];
                 }
             } else {
 #pragma unroll
@@ -219,7 +211,7 @@ k_rollout_st_jac_an(Params p, int B, int N, const double* __restrict__ x0, const
                     for (int i = 0; i < 6; ++i) d[i] = sD[(c * 6 + i) * KA_LD];
                     st_jac_col(J, d, c < 6 ? 0 : c - 5, k);
 #pragma unroll
-                    for (int i = 0; i < 7; ++i) sA[(c * 7 + i) * KA_LD] += wgt * k[i];
+                    for (int i = 0; i < 7; ++i) sA[(i * 8 + c) * KA_LD] += wgt * k[i];
                     if (s < 3) {
 #pragma unroll
                         for (int i = 0; i < 6; ++i) sD[(c * 6 + i) * KA_LD] = (c == i ? 1.0 : 0.0) + cs * k[i];
@@ -227,26 +219,35 @@ k_rollout_st_jac_an(Params p, int B, int N, const double* __restrict__ x0, const
                 }
             }
         }
-        const double h6 = h * (1.0 / 6.0);
+        const double h6 = hh * (1.0 / 6.0);
 #pragma unroll
         for (int i = 0; i < 8; ++i) x[i] = x[i] + h6 * facc[i];
         if (live) {
 #pragma unroll
             for (int i = 0; i < 8; ++i) Xb[(n + 1) * 8 + i] = x[i];
         }
-        sH[tid] = h6;
         __syncwarp();
-        for (int t = 0; t < 32; ++t) {
-            const size_t bt = blk0 + t;
-            if (bt >= (size_t)B) break;
-            const double ht = sH[wbase + t];
-            const double* a = ka_sm + 48 * KA_LD + wbase + t;
-            double* out = AB + (bt * N + n) * 80;
+        // read-out: the warp writes each of its trajectories' 8x10 block as one 640-byte run (acc rows are in output order:
+        // entry (row, col) of the block = acc row i * 8 + c, or a unit-vector entry for row s / columns s, t)
+        int o_src[3];
+        double o_unit[3];
 #pragma unroll
-            for (int q = 0; q < 3; ++q) {
-                const int o = lane + 32 * q;
-                if (o < 80) out[o] = o_src[q] < 0 ? o_unit[q] : o_unit[q] + ht * a[o_src[q] * KA_LD];
-            }
+        for (int q = 0; q < 3; ++q) {
+            const int o = lane + 32 * q, row = o / 10, col = o - row * 10;
+            const int i = row < 4 ? row : (row == IS ? -1 : row - 1);                    // Ux Uy r delta | ey epsi t -> 0..6
+            const int c = col < 4 ? col : ((col == IS || col == IT) ? -1 : (col < IT ? col - 1 : col - 2));   // -> 0..7
+            o_src[q] = (o < 80 && i >= 0 && c >= 0) ? (i * 8 + c) * KA_LD : -1;
+            o_unit[q] = row == col ? 1.0 : 0.0;
+        }
+        const double* a = ka_sm + 48 * KA_LD + wbase;
+        double* out = AB + ((size_t)blk0 * N + n) * 80 + lane;
+#pragma unroll 4
+        for (int t = 0; t < nt; ++t) {
+            const double ht = __shfl_sync(0xffffffffu, h6, t);
+#pragma unroll
+            for (int q = 0; q < 3; ++q)
+                if (lane + 32 * q < 80)
+                    out[(size_t)t * N * 80 + 32 * q] = o_src[q] < 0 ? o_unit[q] : o_unit[q] + ht * a[o_src[q] + t];
         }
         __syncwarp();
     }

@@ -1,0 +1,120 @@
+"""Several batches in flight on one GPU.
+
+A batched NMPC solve ends in a latency-bound tail: after ~50 lock-step passes a few dozen hard instances are left, each
+pass of them costs about a millisecond whatever the batch size, and the GPU idles.  Instances of
+different batches are as independent as instances of one batch (simulation/racing.py:230-241 of the reference steps its
+controllers one after the other with no interaction), so the tail of one batch can run under the full passes of the
+next: every LANE owns a handle (include/vc_api.h: one vc_handle per stream), a non-blocking CUDA stream and its solver
+workspace, and is driven by its own host thread (the C-ABI calls release the GIL).  Step i goes to lane i mod L; a lane
+executes its steps in order.  Results are bit-identical to solving the batches one after the other: a handle never
+shares state with another handle.
+
+`ordered(i)` gives the steps a global order for the sections that need one (a collective over the ranks must be issued
+in the same order by every rank).
+"""
+from __future__ import annotations
+
+import threading
+from typing import Callable, List, Optional, Sequence
+
+
+class Lane:
+    """One handle + stream.  `stream` is a torch.cuda.Stream (None in host-only tests)."""
+
+    def __init__(self, index: int, engine, stream=None):
+        self.index, self.eng, self.stream = index, engine, stream
+        self.buf = {}     # per-lane work buffers of the caller
+
+    def __enter__(self):
+        if self.stream is not None:
+            import torch
+            self._ctx = torch.cuda.stream(self.stream)
+            self._ctx.__enter__()
+        return self
+
+    def __exit__(self, *a):
+        if self.stream is not None:
+            self._ctx.__exit__(*a)
+
+    def synchronize(self):
+        if self.stream is not None:
+            self.stream.synchronize()
+
+
+class InFlight:
+    def __init__(self, lanes: Sequence[Lane]):
+        if not lanes:
+            raise ValueError("InFlight needs at least one lane")
+        self.lanes: List[Lane] = list(lanes)
+        self._cv = threading.Condition()
+        self._next = 0
+
+    @classmethod
+    def create(cls, car_config, mpc_config, track, device: int, n_lanes: int):
+        """n_lanes engines on `device`, each on a non-blocking stream of its own."""
+        import torch
+        from .engine import Engine
+        lanes = []
+        for i in range(n_lanes):
+            st = torch.cuda.Stream(device=device)
+            lanes.append(Lane(i, Engine(car_config, mpc_config, track, device=device, stream=st.cuda_stream), st))
+        return cls(lanes)
+
+    def ordered(self, i: int):
+        """Context manager: the body of step i runs after the bodies of steps 0..i-1 (of this run) have finished."""
+        return _Ordered(self, i)
+
+    def run(self, step_fn: Callable[[Lane, int], None], n_steps: int, first: Optional[Callable[[Lane], None]] = None,
+            last: Optional[Callable[[Lane], None]] = None):
+        """step_fn(lane, i) for i in range(n_steps), step i on lane i mod L, one host thread per lane; `first` / `last`
+        run on every lane (in its stream context) before its first / after its last step.  Returns when every lane has
+        issued all its work (not a device synchronisation).  The first exception of a lane is re-raised."""
+        self._next = 0
+        errors: List[BaseException] = []
+        L = len(self.lanes)
+
+        def loop(lane: Lane):
+            try:
+                with lane:
+                    if first:
+                        first(lane)
+                    for i in range(lane.index, n_steps, L):
+                        step_fn(lane, i)
+                    if last:
+                        last(lane)
+            except BaseException as e:   # noqa: BLE001
+                errors.append(e)
+                with self._cv:            # do not leave the other lanes waiting for this lane's ordered sections
+                    self._next = 1 << 60
+                    self._cv.notify_all()
+
+        threads = [threading.Thread(target=loop, args=(ln,), name=f"vc-lane-{ln.index}") for ln in self.lanes[:max(1, min(L, n_steps))]]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join()
+        if errors:
+            raise errors[0]
+
+    def synchronize(self):
+        for ln in self.lanes:
+            ln.synchronize()
+
+
+class _Ordered:
+    def __init__(self, owner: InFlight, i: int):
+        self.o, self.i = owner, i
+
+    def __enter__(self):
+        with self.o._cv:
+            self.o._cv.wait_for(lambda: self.o._next >= self.i)
+            if self.o._next > self.i:
+                raise RuntimeError("another lane failed")
+        return self
+
+    def __exit__(self, et, ev, tb):
+        with self.o._cv:
+            if et is None:
+                self.o._next = self.i + 1
+            self.o._cv.notify_all()
+        return False
