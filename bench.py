@@ -33,7 +33,7 @@ import bench_common as bc  # noqa: E402
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=8)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default=None, choices=["nmpc", "rollout", "c2"])
@@ -43,7 +43,7 @@ def parse():
     ap.add_argument("--cpu-instances", type=int, default=0, help="instances per step of the CPU arm (0 = default sample)")
     ap.add_argument("--scaling", default="strong", choices=["strong", "weak"],
                     help="strong: the configuration's batch is split over the GPUs; weak: every GPU gets the whole batch")
-    ap.add_argument("--in-flight", type=int, default=3, dest="in_flight",
+    ap.add_argument("--in-flight", type=int, default=4, dest="in_flight",
                     help="C3: batches in flight per GPU (lanes: handle + stream + workspace + host thread each); 1 = one batch at a time")
     ap.add_argument("--lap-cache", default=None, help="npz file to save/load the untimed warm-start lap (profiling runs)")
     ap.add_argument("--rollout-batch", type=int, default=0, help="trajectories of the C5 leg (0 = 1,048,576)")

@@ -222,7 +222,7 @@ def run_nmpc(a, rank, world, local):
     value_single = B_total / (ms_single * 1e-3)
     # ---- the headline: the same K steps with several batches in flight (lane = handle + stream + workspace + host thread;
     # the latency-bound tail of one batch runs under the full passes of the next; results are bit-identical)
-    L = max(1, int(getattr(a, "in_flight", 3)))
+    L = max(1, int(getattr(a, "in_flight", 4)))
     fl = None
     ms, value, launches_fl = ms_single, value_single, None
     if L > 1:

@@ -126,6 +126,23 @@ int vc_horizon_params_tracks(vc_handle* h, int B, const int* d_track_id, const d
                              double* d_ds, double* d_kappa);
 int vc_plant_step_tracks(vc_handle* h, int B, const int* d_track_id, double* d_x, const double* d_u, double dt);
 
+/* replaces: Track.__init__ for a batch of GENERATED tracks, on the device: Track._construct_path
+ * (track.py:254-296: corner polygon -> waypoints every `resolution` m -> centred moving average of half-width `smoothing`,
+ * numpy's summation order), Track._construct_spline (:206-252: not-a-knot cubic B-spline through the waypoints, track
+ * length by the trapezoid rule), Track.get_curvature (:109-119) sampled every 0.05 m and Track._precompute_curvatures
+ * (:156-167: cubic B-spline through that table = Track.k).  h_corners[T][max_corners][2] (host), h_n_corners[T],
+ * h_resolution[T], h_smoothing[T].  The built curvature splines REPLACE the handle's track atlas: track t is then
+ * `track_id == t` in vc_horizon_params_tracks / vc_plant_step_tracks.  Synchronises (two counts are read back to size the
+ * tables).  vc_built_track_info: length / number of waypoints / curvature-table size of built track t.
+ * vc_built_track_read copies a table of track t to the host: what = 0 Track.k coefficients, 1 / 2 smoothed waypoints x / y,
+ * 3 / 4 coefficients of x(u) / y(u), 5 the curvature table.  vc_built_track_rel2glob: (s, ey) -> (cx, cy) on track t, the
+ * obstacle placement of Track._construct_obstacles (:131-138); d_xy[n,2]. */
+int vc_build_tracks(vc_handle* h, int T, int max_corners, const double* h_corners, const int* h_n_corners,
+                    const double* h_resolution, const int* h_smoothing);
+int vc_built_track_info(vc_handle* h, int t, double* length, int* n_waypoints, int* n_k);
+int vc_built_track_read(vc_handle* h, int t, int what, double* h_out, int n);
+int vc_built_track_rel2glob(vc_handle* h, int t, int n, const double* d_s, const double* d_ey, double* d_xy);
+
 /* replaces: the tyre helper Functions car.Fx_f/Fx_r/Fy_f/Fy_r/alpha_f/alpha_r (dynamic_car.py:79-142)
  * for arrays.  d_out[B,6] = Fx_f Fx_r Fy_f Fy_r alpha_f alpha_r. */
 int vc_tyre_forces(vc_handle* h, int B, const double* d_x, const double* d_u, double* d_out);

@@ -1,8 +1,8 @@
 #!/bin/bash
 # Round-2 profiling recipe (run under gpurun on one B200; outputs in gpurun_out/, summaries are copied to profiles/).
-#   tmp_data/c3_lap.npz = warm-start lap (bench_reference.oracle_lap), so that the untimed lap replay is skipped.
+#   tmp_data/lap_cache.npz = warm-start lap (written by bench.py --lap-cache on an earlier run), so that the untimed lap replay is skipped.
 set -u
-B="python bench.py --steps 2 --warmup 3 --no-secondary --no-cpu-baseline --lap-cache tmp_data/c3_lap.npz"
+B="python bench.py --steps 2 --warmup 3 --no-secondary --no-cpu-baseline --in-flight 1 --lap-cache tmp_data/lap_cache.npz"
 $B > gpurun_out/r02_prof_plain.json 2> gpurun_out/r02_prof_plain.err || exit 1
 ncu --metrics gpu__time_duration.sum --clock-control none -c 420 --csv --log-file gpurun_out/r02_launches.csv $B > /dev/null 2>&1
 for k in k_eval_st k_eval_pm 'k_step_a$' 'k_step_b$' k_update; do

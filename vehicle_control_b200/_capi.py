@@ -52,6 +52,10 @@ EXPORTS = {
     "vc_set_track_atlas": (C.c_int, [C.c_void_p, C.c_int, PD, PD, PD, PD]),
     "vc_horizon_params_tracks": (C.c_int, [C.c_void_p, C.c_int, PD, PD, PD, PD, PD]),
     "vc_plant_step_tracks": (C.c_int, [C.c_void_p, C.c_int, PD, PD, PD, D]),
+    "vc_build_tracks": (C.c_int, [C.c_void_p, C.c_int, C.c_int, PD, PD, PD, PD]),
+    "vc_built_track_info": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(D), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "vc_built_track_read": (C.c_int, [C.c_void_p, C.c_int, C.c_int, PD, C.c_int]),
+    "vc_built_track_rel2glob": (C.c_int, [C.c_void_p, C.c_int, C.c_int, PD, PD, PD]),
     "vc_tyre_forces": (C.c_int, [C.c_void_p, C.c_int, PD, PD, PD]),
     "vc_nmpc_solve": (C.c_int, [C.c_void_p, C.c_int, PD, PD, PD, PD, C.c_int, PD, PD, PD, PD, PD, PD]),
     "vc_nmpc_solve_static": (C.c_int, [C.c_void_p, C.c_int, PD, PD, PD, PD, C.c_int, PD, PD, PD, PD, PD, PD]),

@@ -8,7 +8,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libvc_b200.so")
-SOURCES = ["vc_kernels.cu", "vc_solver.cu", "vc_api_host.cu"]
+SOURCES = ["vc_kernels.cu", "vc_solver.cu", "vc_api_host.cu", "vc_track_build.cu"]
 HEADERS = ["vc_ad.cuh", "vc_model.cuh", "vc_jac.cuh", "vc_handle.h", "vc_nlp.cuh", "vc_adj.cuh", os.path.join("..", "..", "include", "vc_api.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "--fmad=true"]

@@ -22,6 +22,11 @@ struct vc_handle {
     double* d_atlas = nullptr;     // concatenated curvature spline coefficients
     void* d_atlas_desc = nullptr;  // [n_atlas] descriptors {x0, dx, offset, n}
     int n_atlas = 0;
+    // tracks built on the device (vc_build_tracks): waypoint / centre-line spline / curvature-table storage
+    double* d_bt = nullptr;        // [wx | wy | cx | cy] each [sum n_wp], then the raw curvature tables [sum n_k]
+    std::vector<int> bt_wp_off, bt_n_wp, bt_k_off, bt_n_k;   // per built track (host copies)
+    std::vector<double> bt_length;
+    long long bt_total_wp = 0, bt_total_k = 0;
     int sm_count = 148;
     int max_smem_optin = 0;
     long long launches = 0;
@@ -44,6 +49,7 @@ struct vc_handle {
 };
 
 namespace vc {
+struct TrackDesc { double x0, dx; int off, n; };   // one curvature table of the atlas: uniform sites x0 + i dx, coefficients at off
 void set_error(const std::string& msg);
 int check_cuda(cudaError_t e, const char* what);
 // launchers implemented in vc_solver.cu

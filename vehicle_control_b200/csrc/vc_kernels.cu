@@ -379,7 +379,6 @@ k_plant_step(Params p, int B, const double* __restrict__ kc, UniformKnots kt, do
 
 // ---- per-instance tracks: a track atlas holds the curvature tables of several tracks; every
 // instance carries a track id.  Same arithmetic as k_horizon_params / k_plant_step, the table chosen per instance.
-struct TrackDesc { double x0, dx; int off, n; };
 
 __global__ void __launch_bounds__(256)
 k_horizon_params_atlas(int B, int N, int M, double mpc_dt, double ds_pm, const double* __restrict__ atlas,
@@ -498,7 +497,7 @@ int vc_destroy(vc_handle* h) {
     if (!h) return 0;
     cudaSetDevice(h->device);
     cudaFree(h->d_kc); cudaFree(h->d_xc); cudaFree(h->d_yc); cudaFree(h->d_scratch);
-    cudaFree(h->d_atlas); cudaFree(h->d_atlas_desc);
+    cudaFree(h->d_atlas); cudaFree(h->d_atlas_desc); cudaFree(h->d_bt);
     cudaFree(h->d_ws); cudaFree(h->d_active);
     if (h->h_active) cudaFreeHost(h->h_active);
     delete h;

@@ -116,6 +116,46 @@ class Engine:
                                           step.ctypes.data), "vc_set_track_atlas")
         self.tracks = list(tracks)
 
+    def build_tracks(self, track_configs):
+        """Track construction ON THE DEVICE for a list of track configs (corners / resolution / smoothing, the keys of
+        config/environment/*.yaml): waypoints, smoothing, centre-line splines, length, curvature table and Track.k of every
+        track (include/vc_api.h: vc_build_tracks).  The built tracks become the atlas: track_id = position in the list.
+        Returns one dict per track: length, n_waypoints, n_k."""
+        cfgs = [as_config(c) for c in track_configs]
+        T = len(cfgs)
+        mc = max(len(c.corners) for c in cfgs)
+        corners = np.zeros((T, mc, 2))
+        for t, c in enumerate(cfgs):
+            corners[t, :len(c.corners)] = np.asarray([[float(p[0]), float(p[1])] for p in c.corners])
+        nc = np.ascontiguousarray([len(c.corners) for c in cfgs], dtype=np.int32)
+        res = np.ascontiguousarray([float(c.resolution) for c in cfgs], dtype=np.float64)
+        sm = np.ascontiguousarray([int(c.smoothing) for c in cfgs], dtype=np.int32)
+        check(self.lib.vc_build_tracks(self._h, T, mc, corners.ctypes.data, nc.ctypes.data, res.ctypes.data, sm.ctypes.data),
+              "vc_build_tracks")
+        out = []
+        for t in range(T):
+            L, nw, nk = C.c_double(), C.c_int(), C.c_int()
+            check(self.lib.vc_built_track_info(self._h, t, C.byref(L), C.byref(nw), C.byref(nk)), "vc_built_track_info")
+            out.append({"length": L.value, "n_waypoints": nw.value, "n_k": nk.value})
+        self.built_tracks = out
+        return out
+
+    BUILT_TABLES = {"k_coefs": 0, "waypoints_x": 1, "waypoints_y": 2, "x_coefs": 3, "y_coefs": 4, "curvature_table": 5}
+
+    def built_track_table(self, t, name):
+        info = self.built_tracks[t]
+        n = info["n_k"] if name in ("k_coefs", "curvature_table") else info["n_waypoints"]
+        out = np.empty(n)
+        check(self.lib.vc_built_track_read(self._h, int(t), self.BUILT_TABLES[name], out.ctypes.data, n), "vc_built_track_read")
+        return out
+
+    def built_track_rel2glob(self, t, s, ey):
+        """(s, ey) -> (cx, cy) on built track t (obstacle placement, track.py:131-138)."""
+        out = self.empty(s.numel(), 2)
+        check(self.lib.vc_built_track_rel2glob(self._h, int(t), s.numel(), self._p(s), self._p(ey), self._p(out)),
+              "vc_built_track_rel2glob")
+        return out
+
     @property
     def H(self):
         return self.cfg.N + self.cfg.M
