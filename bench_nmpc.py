@@ -28,6 +28,8 @@ def controller_config(horizon_pm=35, obstacles=True, max_speed=18):
     # reference leaves them, except the iteration limit (IPOPT 3000): a handful of the 65,536 perturbed instances crawl
     # along an obstacle pole for ~1000 iterations under IPOPT's algorithm without its restoration phase
     c["solver"] = {"max_iter": MAX_ITER}
+    if os.environ.get("VC_BENCH_WIDE_MAX"):     # tuning runs: instances left below which a whole CTA serves one instance
+        c["solver"]["wide_max"] = int(os.environ["VC_BENCH_WIDE_MAX"])
     return c
 
 
@@ -226,7 +228,16 @@ def run_nmpc(a, rank, world, local):
     fl = None
     ms, value, launches_fl = ms_single, value_single, None
     if L > 1:
-        fl = InFlight.create(bc.load_yaml("models/dynamic_car.yaml"), cfg, tr, local, L)
+        # lanes spin while they wait for the GPU when every waiting thread of the box can have a core, else they sleep
+        try:
+            cores = len(os.sched_getaffinity(0))
+        except AttributeError:
+            cores = os.cpu_count() or 1
+        ranks_here = int(os.environ.get("LOCAL_WORLD_SIZE", world))
+        blocking = (L + 1) * ranks_here > cores
+        if os.environ.get("VC_BENCH_SPIN") is not None:
+            blocking = os.environ["VC_BENCH_SPIN"] == "0"
+        fl = InFlight.create(bc.load_yaml("models/dynamic_car.yaml"), cfg, tr, local, L, blocking_sync=blocking)
         for ln in fl.lanes:
             with ln:
                 ln.buf = {"X": torch.empty_like(Xw), "U": torch.empty_like(Uw), "ds": eng.empty(B, H), "kap": eng.empty(B, H),
@@ -365,6 +376,7 @@ def run_nmpc(a, rank, world, local):
                    "batch_total": B_total, "batch_per_gpu": B, "in_flight_batches": L,
                    "in_flight": ("step i runs on lane i mod %d (handle + stream + workspace + host thread each): the latency-bound tail of "
                                  "one batch overlaps the full passes of the next; results bit-identical to single-batch solves" % L) if fl is not None else "one batch at a time",
+                   "host_wait": None if fl is None else ("sleep on a blocking-sync event" if blocking else "spin"),
                    "N": N, "M": M, "n_obstacles": int(obh.shape[1]), "tol": 1e-8,
                    "solver": {"max_iter": MAX_ITER, "max_soc": 4, "watchdog_trigger": 10, "note": "same on the CPU arm"},
                    "result_gather": "all_gather of (u0, obj, status, iters) inside the timed step" if strong and world > 1 else "none (one rank)" if world == 1 else "none (weak scaling)",

@@ -11,7 +11,8 @@
  *   - work is enqueued on the handle's CUDA stream.  The rollout / track / plant entry points are asynchronous;
  *     vc_nmpc_solve is NOT: its interior-point loop reads the number of unfinished instances back once per pass
  *     (a 4-byte copy + stream synchronisation) to size the next launches, so it returns with the results complete.
- *     A handle is bound to one device and is not re-entrant.
+ *     A handle is bound to one device and is not re-entrant; handles are independent of each other, so several batches
+ *     can be in flight on one GPU, one handle (on its own stream) and one host thread each.
  *   - state order  SingleTrack: Ux Uy r delta s ey epsi t   (models/dynamic_car.py:246-247)
  *                  PointMass  : V s ey epsi t              (models/dynamic_point_mass.py:155-156)
  *     input order  SingleTrack: Fx w ; PointMass: Fx Fy     (dynamic_car.py:208-209, dynamic_point_mass.py:120-121)
@@ -186,6 +187,12 @@ int vc_nmpc_solve_host(vc_handle* h, int B, const double* h_x0, const double* h_
  * h_obst[B,n_obs,3] or NULL; h_X[B,8,H] / h_U[B,2,H]: previous prediction in (the warm start), solution out.  Synchronises. */
 int vc_nmpc_command_host(vc_handle* h, int B, const double* h_x0, const double* h_obst, int n_obs, double* h_X, double* h_U,
                          double* h_obj, int* h_status, int* h_iters, double* h_kkt);
+
+/* How the host waits inside vc_nmpc_solve / vc_nmpc_*_host (no reference counterpart: the reference's solve is host code).
+ * 0 (default): spin on the stream (lowest latency: a single vehicle's tick).  1: sleep on a blocking-sync event -- for
+ * several handles in flight, each driven by its own host thread (vehicle_control_b200/pipeline.py), when there are fewer
+ * cores than waiting threads (8 ranks x 4 lanes on one box). */
+int vc_set_blocking_sync(vc_handle* h, int on);
 
 /* Measurement hooks (no reference counterpart; the reference times command() with time.time(), racing.py:231-233):
  * with profiling on, vc_nmpc_solve brackets every kernel of its iteration loop with CUDA events on the handle's

@@ -61,6 +61,7 @@ EXPORTS = {
     "vc_nmpc_solve_static": (C.c_int, [C.c_void_p, C.c_int, PD, PD, PD, PD, C.c_int, PD, PD, PD, PD, PD, PD]),
     "vc_nmpc_eval": (C.c_int, [C.c_void_p, C.c_int, PD, PD, PD, PD, C.c_int, PD, PD, PD]),
     "vc_nmpc_solve_host": (C.c_int, [C.c_void_p, C.c_int, PD, PD, PD, PD, C.c_int, PD, PD, PD, PD, PD, PD]),
+    "vc_set_blocking_sync": (C.c_int, [C.c_void_p, C.c_int]),
     "vc_nmpc_command_host": (C.c_int, [C.c_void_p, C.c_int, PD, PD, C.c_int, PD, PD, PD, PD, PD, PD]),
     "vc_set_profiling": (C.c_int, [C.c_void_p, C.c_int]),
     "vc_get_profile": (C.c_int, [C.c_void_p, PD, PD, PD]),

@@ -69,7 +69,7 @@ int vc_nmpc_solve_host(vc_handle* h, int B, const double* h_x0, const double* h_
     if (h_kkt) cudaMemcpyAsync(h_kkt, d + o_kkt, nB * sizeof(double), cudaMemcpyDeviceToHost, st);
     if (h_status) cudaMemcpyAsync(h_status, d_status, nB * sizeof(int), cudaMemcpyDeviceToHost, st);
     if (h_iters) cudaMemcpyAsync(h_iters, d_iters, nB * sizeof(int), cudaMemcpyDeviceToHost, st);
-    return check_cuda(cudaStreamSynchronize(st), "vc_nmpc_solve_host");
+    return check_cuda(stream_wait(h), "vc_nmpc_solve_host");
 }
 
 // CascadedMPC.command() for a batch, host buffers in and out: _init_horizon on the device (needs vc_set_track), the
@@ -113,12 +113,18 @@ int vc_nmpc_command_host(vc_handle* h, int B, const double* h_x0, const double* 
     if (h_kkt) cudaMemcpyAsync(h_kkt, d + o_kkt, nB * sizeof(double), cudaMemcpyDeviceToHost, st);
     if (h_status) cudaMemcpyAsync(h_status, d_status, nB * sizeof(int), cudaMemcpyDeviceToHost, st);
     if (h_iters) cudaMemcpyAsync(h_iters, d_iters, nB * sizeof(int), cudaMemcpyDeviceToHost, st);
-    return check_cuda(cudaStreamSynchronize(st), "vc_nmpc_command_host");
+    return check_cuda(stream_wait(h), "vc_nmpc_command_host");
 }
 
 int vc_nmpc_debug_read(vc_handle* h, int b, int array, double* h_out, int n) {
     if (!h || !h_out) { set_error("vc_nmpc_debug_read: null argument"); return -1; }
     return debug_read(h, b, array, h_out, n);
+}
+
+int vc_set_blocking_sync(vc_handle* h, int on) {
+    if (!h) { set_error("vc_set_blocking_sync: null handle"); return -1; }
+    h->blocking_sync = on ? 1 : 0;
+    return 0;
 }
 
 long long vc_workspace_bytes(vc_handle* h) { return h ? (long long)h->ws_bytes : 0; }

@@ -39,6 +39,10 @@ struct vc_handle {
     int* d_active = nullptr;   // [2] counters + 2 x [active_cap] compacted instance lists
     int active_cap = 0;
     int* h_active = nullptr;
+    // host waits of the solver loop: 0 = spin (cudaStreamSynchronize, lowest latency), 1 = sleep on a blocking-sync event
+    // (vc_set_blocking_sync: for several handles driven by more host threads than there are cores to spin on)
+    int blocking_sync = 0;
+    cudaEvent_t sync_event = nullptr;
     int last_passes = 0;
     // optional per-kernel timing of the solver loop (vc_set_profiling)
     int profiling = 0;
@@ -52,6 +56,17 @@ namespace vc {
 struct TrackDesc { double x0, dx; int off, n; };   // one curvature table of the atlas: uniform sites x0 + i dx, coefficients at off
 void set_error(const std::string& msg);
 int check_cuda(cudaError_t e, const char* what);
+// wait until everything enqueued on the handle's stream has finished (spinning or sleeping, see vc_handle::blocking_sync)
+inline cudaError_t stream_wait(vc_handle* h) {
+    if (!h->blocking_sync) return cudaStreamSynchronize(h->stream);
+    if (!h->sync_event) {
+        cudaError_t e = cudaEventCreateWithFlags(&h->sync_event, cudaEventBlockingSync | cudaEventDisableTiming);
+        if (e != cudaSuccess) return e;
+    }
+    cudaError_t e = cudaEventRecord(h->sync_event, h->stream);
+    if (e != cudaSuccess) return e;
+    return cudaEventSynchronize(h->sync_event);
+}
 // launchers implemented in vc_solver.cu
 int launch_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_kappa, const double* d_ds,
                       const double* d_obst, int n_obs, double* d_X, double* d_U, double* d_obj, int* d_status,

@@ -500,6 +500,7 @@ int vc_destroy(vc_handle* h) {
     cudaFree(h->d_atlas); cudaFree(h->d_atlas_desc); cudaFree(h->d_bt);
     cudaFree(h->d_ws); cudaFree(h->d_active);
     if (h->h_active) cudaFreeHost(h->h_active);
+    if (h->sync_event) cudaEventDestroy(h->sync_event);
     delete h;
     return 0;
 }

@@ -1920,7 +1920,7 @@ int launch_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_k
         }
         if (pass >= 3) {   // no instance can finish before its third pass (init, >= 1 step, convergence test)
             cudaMemcpyAsync(h->h_active, counts[cur], sizeof(int), cudaMemcpyDeviceToHost, st);
-            rc = check_cuda(cudaStreamSynchronize(st), "nmpc iteration");
+            rc = check_cuda(stream_wait(h), "nmpc iteration");
             if (rc) return rc;
             n_act = *h->h_active;
             if (n_act == 0) break;

@@ -315,6 +315,10 @@ class Engine:
                                             iters.ctypes.data, kkt.ctypes.data), "vc_nmpc_command_host")
         return {"obj": obj, "status": status, "iters": iters, "kkt": kkt}
 
+    def set_blocking_sync(self, on: bool):
+        """Host waits of the solve sleep on a blocking-sync event instead of spinning (include/vc_api.h)."""
+        check(self.lib.vc_set_blocking_sync(self._h, 1 if on else 0), "vc_set_blocking_sync")
+
     def set_profiling(self, on: bool):
         check(self.lib.vc_set_profiling(self._h, 1 if on else 0), "vc_set_profiling")
 

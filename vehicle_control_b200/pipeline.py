@@ -50,14 +50,16 @@ class InFlight:
         self._next = 0
 
     @classmethod
-    def create(cls, car_config, mpc_config, track, device: int, n_lanes: int):
-        """n_lanes engines on `device`, each on a non-blocking stream of its own."""
+    def create(cls, car_config, mpc_config, track, device: int, n_lanes: int, blocking_sync: bool = True):
+        """n_lanes engines on `device`, each on a non-blocking stream of its own.  blocking_sync: the lanes' host threads
+        sleep while they wait for the GPU instead of spinning (there may be more lanes x ranks than cores)."""
         import torch
         from .engine import Engine
         lanes = []
         for i in range(n_lanes):
             st = torch.cuda.Stream(device=device)
             lanes.append(Lane(i, Engine(car_config, mpc_config, track, device=device, stream=st.cuda_stream), st))
+            lanes[-1].eng.set_blocking_sync(blocking_sync)
         return cls(lanes)
 
     def ordered(self, i: int):
