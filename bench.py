@@ -43,8 +43,10 @@ def parse():
     ap.add_argument("--cpu-instances", type=int, default=0, help="instances per step of the CPU arm (0 = default sample)")
     ap.add_argument("--scaling", default="strong", choices=["strong", "weak"],
                     help="strong: the configuration's batch is split over the GPUs; weak: every GPU gets the whole batch")
-    ap.add_argument("--in-flight", type=int, default=4, dest="in_flight",
-                    help="C3: batches in flight per GPU (lanes: handle + stream + workspace + host thread each); 1 = one batch at a time")
+    ap.add_argument("--in-flight", type=int, default=0, dest="in_flight",
+                    help="C3: batches in flight per GPU (lanes: handle + stream + workspace + host thread each); 1 = one batch "
+                         "at a time; 0 = by the per-GPU batch (4 at >= 32,768 instances, 6 at >= 16,384, else 8: the tail of a "
+                         "batch lasts as long whatever its size, so smaller batches need more of them in flight to hide it)")
     ap.add_argument("--lap-cache", default=None, help="npz file to save/load the untimed warm-start lap (profiling runs)")
     ap.add_argument("--rollout-batch", type=int, default=0, help="trajectories of the C5 leg (0 = 1,048,576)")
     ap.add_argument("--no-secondary", action="store_true", help="skip the C5 block of the default line")
@@ -53,11 +55,17 @@ def parse():
 
 def main():
     a = parse()
+    # ONE JSON line on stdout is the contract: whatever libraries print to fd 1 (NCCL's version banner / debug lines, a
+    # stray print) is sent to stderr for the whole run, and the line is written to the saved descriptor at the end
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    emit = lambda obj: os.write(real_stdout, (json.dumps(obj) + "\n").encode())
     a.warmup = max(a.warmup, 3) if a.impl == "b200" else a.warmup
     workload = a.workload or bc.default_workload()
     if a.impl == "reference":
         from bench_reference import run_reference
-        return run_reference(a, workload)
+        return run_reference(a, workload, emit)
     import torch
     rank, world, local = bc.dist_setup(a.gpus)
     torch.cuda.set_device(local)
@@ -79,7 +87,7 @@ def main():
             line["secondary"] = {"rollout": {k: r[k] for k in ("metric", "value", "unit", "ms_per_step", "steps", "warmup", "scaling",
                                                                 "config", "e2e", "roofline", "gpu_launches", "clocks", "cpu_baseline") if k in r}}
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
     bc.dist_teardown()
 
 

@@ -224,7 +224,9 @@ def run_nmpc(a, rank, world, local):
     value_single = B_total / (ms_single * 1e-3)
     # ---- the headline: the same K steps with several batches in flight (lane = handle + stream + workspace + host thread;
     # the latency-bound tail of one batch runs under the full passes of the next; results are bit-identical)
-    L = max(1, int(getattr(a, "in_flight", 4)))
+    L = int(getattr(a, "in_flight", 0))
+    if L <= 0:
+        L = 4 if B >= 32768 else (6 if B >= 16384 else 8)
     fl = None
     ms, value, launches_fl = ms_single, value_single, None
     if L > 1:

@@ -127,7 +127,7 @@ def cpu_baseline_nmpc(cfg, sample, gpu_U=None, gpu_obj=None):
     return out
 
 
-def run_reference(a, workload):
+def run_reference(a, workload, emit=None):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
@@ -172,5 +172,5 @@ def run_reference(a, workload):
             "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": {"workload": wl}, "gpu_launches": 0,
             "cpu_baseline": dict({"value": value, "unit": unit, "cores": th, "kind": "port-cpp", "sample": sample}, **extra),
             "e2e": {"value": value, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    (emit or (lambda obj: print(json.dumps(obj), flush=True)))(line)
     return 0
