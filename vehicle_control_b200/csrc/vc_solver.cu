@@ -197,11 +197,17 @@ __global__ void k_prepare(Prob pr, Ws ws, int* list0, int* count0) {
 // forward in Dual1 arithmetic seeded along a (column a of the dynamics / inequality Jacobians) and the hand-written
 // adjoint sweep of vc_adj.cuh in the same arithmetic (gradient of the stage Lagrangian + column a of its exact Hessian);
 // the Gauss-Newton part Jc^T (z/s) Jc is assembled from the eight Jacobian columns with warp shuffles.
+// 256 threads x 2 CTAs per SM (128 registers): the kernel is ~158 KB of straight-line code that every warp runs once, so
+// instruction fetch is its top stall (ncu: "no instruction"); warps of one CTA start together and share the fetches:
+// 12.1 ms per full pass against 14.2 (128 x 4), 16.6 (64 x 8), 12.4 (512 x 1)
 #ifndef VC_EVAL_MINBLOCKS
-#define VC_EVAL_MINBLOCKS 4
+#define VC_EVAL_MINBLOCKS 2
+#endif
+#ifndef VC_EVAL_TPB
+#define VC_EVAL_TPB 256
 #endif
 constexpr int EVAL_ST_LANES = 8;
-__global__ void __launch_bounds__(128, VC_EVAL_MINBLOCKS) k_eval_st(Prob pr, Ws ws) {
+__global__ void __launch_bounds__(VC_EVAL_TPB, VC_EVAL_MINBLOCKS) k_eval_st(Prob pr, Ws ws) {
     const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const int N = pr.N;
     const bool live = t < (long long)(*pr.act_count) * N * EVAL_ST_LANES;
@@ -1654,9 +1660,13 @@ __device__ void step_part_b(const Prob& pr, const Ws& ws, WarpSm& sm, int b, int
 
 // the two halves of an iteration as separate kernels: the factorisation half needs half the registers of the
 // line-search half (no model code), so it runs at twice the occupancy
-__global__ void __launch_bounds__(32 * STEP_WARPS, 4) k_step_a(Prob pr, Ws ws) {
-    __shared__ WarpSm s_all[STEP_WARPS];
-    __shared__ KindTab s_tabs[NKIND];
+#ifndef VC_STEPA_MINBLOCKS
+#define VC_STEPA_MINBLOCKS 4
+#endif
+__global__ void __launch_bounds__(32 * STEP_WARPS, VC_STEPA_MINBLOCKS) k_step_a(Prob pr, Ws ws) {
+    extern __shared__ __align__(16) unsigned char step_smem[];   // WarpSm[STEP_WARPS] | KindTab[NKIND] (> 48 KB at 8 warps)
+    WarpSm* s_all = reinterpret_cast<WarpSm*>(step_smem);
+    KindTab* s_tabs = reinterpret_cast<KindTab*>(step_smem + sizeof(WarpSm) * STEP_WARPS);
     build_kind_tables(pr, s_tabs, threadIdx.x, blockDim.x);
     __syncthreads();
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -1665,8 +1675,9 @@ __global__ void __launch_bounds__(32 * STEP_WARPS, 4) k_step_a(Prob pr, Ws ws) {
     step_part_a(pr, ws, s_all[wid], pr.act_list[i], lane, Group{lane, 32, nullptr, s_tabs});
 }
 __global__ void __launch_bounds__(32 * STEP_WARPS, VC_STEP_MINBLOCKS) k_step_b(Prob pr, Ws ws, int* next_list, int* next_count) {
-    __shared__ WarpSm s_all[STEP_WARPS];
-    __shared__ KindTab s_tabs[NKIND];
+    extern __shared__ __align__(16) unsigned char step_smem[];
+    WarpSm* s_all = reinterpret_cast<WarpSm*>(step_smem);
+    KindTab* s_tabs = reinterpret_cast<KindTab*>(step_smem + sizeof(WarpSm) * STEP_WARPS);
     build_kind_tables(pr, s_tabs, threadIdx.x, blockDim.x);
     __syncthreads();
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -1799,6 +1810,12 @@ __global__ void __launch_bounds__(128) k_nmpc_eval(Prob pr, const double* X, con
 
 // ------------------------------------------------------------------------------------------------
 // host side
+constexpr size_t STEP_SMEM = sizeof(WarpSm) * STEP_WARPS + sizeof(KindTab) * NKIND;
+static int step_kernels_smem_optin() {   // dynamic shared memory beyond 48 KB needs the opt-in, once per device context
+    int rc = check_cuda(cudaFuncSetAttribute(k_step_a, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)STEP_SMEM), "cudaFuncSetAttribute(k_step_a)");
+    if (rc) return rc;
+    return check_cuda(cudaFuncSetAttribute(k_step_b, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)STEP_SMEM), "cudaFuncSetAttribute(k_step_b)");
+}
 static int fill_prob(vc_handle* h, Prob& pr, int B, const double* d_x0, const double* d_kappa, const double* d_ds,
                      const double* d_obst, int n_obs) {
     if (h->cfg.N < 1 || h->cfg.M < 0) { set_error("nmpc: config not set (need horizon N >= 1, M >= 0)"); return -1; }
@@ -1843,6 +1860,8 @@ int launch_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_k
     if (!d_X || !d_U) { set_error("nmpc: null X/U pointer"); return -1; }
     pr.X = d_X; pr.U = d_U; pr.obj = d_obj; pr.kkt = d_kkt; pr.status = d_status; pr.iters = d_iters;
     cudaSetDevice(h->device);
+    rc = step_kernels_smem_optin();
+    if (rc) return rc;
     Ws ws;
     ws.H = pr.H;
     ws.stride = (size_t)WS_PER_STAGE * pr.H + NSCAL;
@@ -1892,7 +1911,7 @@ int launch_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_k
         pr.act_list = lists[cur]; pr.act_count = counts[cur];
         if (prof) h->prof_instance_passes += n_act;
         mark();
-        k_eval_st<<<(unsigned)((t_st + 127) / 128), 128, 0, st>>>(pr, ws);
+        k_eval_st<<<(unsigned)((t_st + VC_EVAL_TPB - 1) / VC_EVAL_TPB), VC_EVAL_TPB, 0, st>>>(pr, ws);
         mark();
         if (pr.M > 0) k_eval_pm<<<(unsigned)((t_pm + 127) / 128), 128, 0, st>>>(pr, ws);
         cudaMemsetAsync(counts[1 - cur], 0, sizeof(int), st);
@@ -1902,9 +1921,9 @@ int launch_nmpc_solve(vc_handle* h, int B, const double* d_x0, const double* d_k
             if (trace) mark();
             k_step_b_wide<<<n_act, 32 * LS_TRIALS, 0, st>>>(pr, ws, lists[1 - cur], counts[1 - cur]);
         } else {
-            k_step_a<<<(n_act + STEP_WARPS - 1) / STEP_WARPS, 32 * STEP_WARPS, 0, st>>>(pr, ws);
+            k_step_a<<<(n_act + STEP_WARPS - 1) / STEP_WARPS, 32 * STEP_WARPS, STEP_SMEM, st>>>(pr, ws);
             if (trace) mark();
-            k_step_b<<<(n_act + STEP_WARPS - 1) / STEP_WARPS, 32 * STEP_WARPS, 0, st>>>(pr, ws, lists[1 - cur], counts[1 - cur]);
+            k_step_b<<<(n_act + STEP_WARPS - 1) / STEP_WARPS, 32 * STEP_WARPS, STEP_SMEM, st>>>(pr, ws, lists[1 - cur], counts[1 - cur]);
         }
         k_update<<<(unsigned)(((long long)n_act * pr.H * 32 + 127) / 128), 128, 0, st>>>(pr, ws);
         mark();
@@ -2004,6 +2023,8 @@ int launch_nmpc_solve_static(vc_handle* h, int B, const double* d_x0, const doub
     rc = static_scratch_address(h->device, &scratch);
     if (rc) return rc;
     cudaSetDevice(h->device);
+    rc = step_kernels_smem_optin();
+    if (rc) return rc;
     ws.base = (double*)scratch;
     int* act = (int*)(scratch + ws_bytes);
     int* counts[2] = {act, act + 1};
@@ -2017,15 +2038,15 @@ int launch_nmpc_solve_static(vc_handle* h, int B, const double* d_x0, const doub
     for (; pass < max_pass; ++pass) {
         const long long t_st = (long long)n_act * pr.N * EVAL_ST_LANES, t_pm = (long long)n_act * pr.M * 15;
         pr.act_list = lists[cur]; pr.act_count = counts[cur];
-        k_eval_st<<<(unsigned)((t_st + 127) / 128), 128, 0, st>>>(pr, ws);
+        k_eval_st<<<(unsigned)((t_st + VC_EVAL_TPB - 1) / VC_EVAL_TPB), VC_EVAL_TPB, 0, st>>>(pr, ws);
         if (pr.M > 0) k_eval_pm<<<(unsigned)((t_pm + 127) / 128), 128, 0, st>>>(pr, ws);
         cudaMemsetAsync(counts[1 - cur], 0, sizeof(int), st);
         if (n_act <= wide_max) {
             k_step_a_wide<<<n_act, WIDE_NT, 0, st>>>(pr, ws);
             k_step_b_wide<<<n_act, 32 * LS_TRIALS, 0, st>>>(pr, ws, lists[1 - cur], counts[1 - cur]);
         } else {
-            k_step_a<<<(n_act + STEP_WARPS - 1) / STEP_WARPS, 32 * STEP_WARPS, 0, st>>>(pr, ws);
-            k_step_b<<<(n_act + STEP_WARPS - 1) / STEP_WARPS, 32 * STEP_WARPS, 0, st>>>(pr, ws, lists[1 - cur], counts[1 - cur]);
+            k_step_a<<<(n_act + STEP_WARPS - 1) / STEP_WARPS, 32 * STEP_WARPS, STEP_SMEM, st>>>(pr, ws);
+            k_step_b<<<(n_act + STEP_WARPS - 1) / STEP_WARPS, 32 * STEP_WARPS, STEP_SMEM, st>>>(pr, ws, lists[1 - cur], counts[1 - cur]);
         }
         k_update<<<(unsigned)(((long long)n_act * pr.H * 32 + 127) / 128), 128, 0, st>>>(pr, ws);
         cur = 1 - cur;
