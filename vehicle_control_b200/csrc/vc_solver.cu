@@ -197,14 +197,14 @@ __global__ void k_prepare(Prob pr, Ws ws, int* list0, int* count0) {
 // forward in Dual1 arithmetic seeded along a (column a of the dynamics / inequality Jacobians) and the hand-written
 // adjoint sweep of vc_adj.cuh in the same arithmetic (gradient of the stage Lagrangian + column a of its exact Hessian);
 // the Gauss-Newton part Jc^T (z/s) Jc is assembled from the eight Jacobian columns with warp shuffles.
-// 256 threads x 2 CTAs per SM (128 registers): the kernel is ~158 KB of straight-line code that every warp runs once, so
+// 192 threads x 2 CTAs per SM (170 registers): the kernel is ~158 KB of straight-line code that every warp runs once, so
 // instruction fetch is its top stall (ncu: "no instruction"); warps of one CTA start together and share the fetches:
-// 12.1 ms per full pass against 14.2 (128 x 4), 16.6 (64 x 8), 12.4 (512 x 1)
+// 11.8 ms per full pass against 14.2 (128 x 4), 16.6 (64 x 8), 12.1 (256 x 2), 12.0 (384 x 1), 12.4 (512 x 1)
 #ifndef VC_EVAL_MINBLOCKS
 #define VC_EVAL_MINBLOCKS 2
 #endif
 #ifndef VC_EVAL_TPB
-#define VC_EVAL_TPB 256
+#define VC_EVAL_TPB 192
 #endif
 constexpr int EVAL_ST_LANES = 8;
 __global__ void __launch_bounds__(VC_EVAL_TPB, VC_EVAL_MINBLOCKS) k_eval_st(Prob pr, Ws ws) {
