@@ -238,3 +238,45 @@ def test_iteration_limit_is_reported_for_every_instance(golden):
     assert (out["status"] == 2).all() and (out["iters"] == 3).all()
     assert np.isfinite(out["obj"]).all() and np.isfinite(X[:, :, :eng.cfg.N]).all() and np.isfinite(U).all()
     assert not np.array_equal(U[0], f["U0"])      # three steps were taken
+
+
+@pytest.mark.parametrize("run_key,min_1e6,max_branch", [("singletrack2_ippodromo/singletrack", 1.0, 0),
+                                                        ("cascaded4_ippodromo/cascaded", 0.93, 12)])
+def test_follow_mode_per_tick_parity_with_ipopt(golden, run_key, min_1e6, max_branch):
+    """Per-tick parity with IPOPT over a WHOLE saved lap, on the CUDA path (the GPU counterpart of
+    profiles/r02_branch_ticks.md).  Follow mode: every tick starts from the reference's own saved state, the warm start is
+    our previous solution (cascaded_mpc.py:316-338), and the first action is compared with IPOPT's saved one
+    (action_traj[k+1]).  The singletrack lap must agree on EVERY tick; on the cascaded 20+35 lap at least 93 % of the ticks
+    agree to 1e-6 and at most 12 ticks (two short branch clusters of the non-convex NLP, listed in the profile) differ
+    by more than 1e-3."""
+    from vehicle_control_b200.controllers.mpc.cascaded_mpc import cold_guess
+    z, meta = golden
+    m = meta[run_key]
+    eng = _engine(run_key, golden)
+    N, H = eng.cfg.N, eng.H
+    S, A = z[run_key + "/state"], z[run_key + "/action"]
+    X0, U0 = cold_guess(N, H, rng_draw=np.random.RandomState(31).random_sample((2, H)))
+    X, U = eng.tensor(X0[None]), eng.tensor(U0[None])
+    ob = None
+    if m["config"].get("obstacles"):
+        oa = eng.track.obstacle_array()
+        ob = eng.tensor(oa[None]) if len(oa) else None
+    err, iters = [], []
+    for k in range(len(A) - 1):
+        x = eng.tensor(S[k][None])
+        Xk, Uk = X.clone(), U.clone()
+        ds, kap = eng.horizon_params(x, Xk)
+        out = eng.solve(x, kap, ds, Xk, Uk, obstacles=ob)
+        if int(out["status"][0]) > 1:
+            err.append(np.inf)           # keep the warm start, as the survey does
+            continue
+        u = Uk[0, :, 0].cpu().numpy()
+        err.append(float((np.abs(u - A[k + 1]) / np.maximum(1.0, np.abs(A[k + 1]))).max()))
+        iters.append(int(out["iters"][0]))
+        X, U = Xk, Uk
+    err = np.array(err)
+    frac = float((err <= 1e-6).mean())
+    big = int((err > 1e-3).sum())
+    print(f"{run_key}: {len(err)} ticks, {100 * frac:.1f} % within 1e-6 of IPOPT, {int((err <= 1e-5).sum())} within 1e-5, {big} beyond 1e-3 "
+          f"(ticks {np.flatnonzero(err > 1e-3).tolist()}), mean iterations {np.mean(iters):.1f}")
+    assert frac >= min_1e6 and big <= max_branch
