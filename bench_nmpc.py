@@ -143,7 +143,7 @@ def ncu_units():
     return u
 
 
-def time_in_flight(fl, step_fn, steps, warmup):
+def time_in_flight(fl, step_fn, steps, warmup, stagger_s=0.0):
     """K steps over the lanes of `fl` (step i on lane i mod L, vehicle_control_b200/pipeline.py) between barrier +
     synchronize on both sides; device time from a start event to the last lane's end event, max over ranks."""
     import torch
@@ -161,7 +161,7 @@ def time_in_flight(fl, step_fn, steps, warmup):
 
     start = torch.cuda.Event(enable_timing=True)
     start.record(fl.lanes[0].stream)     # nothing is pending anywhere: the time stamp is "now"
-    fl.run(step_fn, steps, last=last)
+    fl.run(step_fn, steps, last=last, stagger_s=stagger_s)
     torch.cuda.synchronize()
     bc.barrier()
     torch.cuda.synchronize()
@@ -260,7 +260,10 @@ def run_nmpc(a, rank, world, local):
         fl.run(fstep, L)                   # allocates every lane's workspace
         lf0 = sum(ln.eng.launch_count() for ln in fl.lanes)
         with bc.ClockSampler(local) as clk:
-            total_fl = time_in_flight(fl, fstep, a.steps, max(a.warmup, L))
+            # offsetting the lanes' starts (pipeline.py: stagger_s) was measured at 0 / 100 / 150 / 200 / 300 ms: no effect
+            # (663 ms per batch each time) -- the lanes are bound by the GPU's throughput, not by their phase
+            stagger = float(os.environ.get("VC_BENCH_STAGGER", 0.0))
+            total_fl = time_in_flight(fl, fstep, a.steps, max(a.warmup, L), stagger_s=stagger)
         launches_fl = sum(ln.eng.launch_count() for ln in fl.lanes) - lf0
         ms = total_fl / a.steps
         value = B_total / (ms * 1e-3)
@@ -314,7 +317,7 @@ def run_nmpc(a, rank, world, local):
         torch.cuda.synchronize()
         bc.barrier()
         t1 = time.perf_counter()
-        fl.run(estep, e2e_steps)          # vc_nmpc_command_host returns after its D2H copies have completed
+        fl.run(estep, e2e_steps, stagger_s=stagger)   # vc_nmpc_command_host returns after its D2H copies have completed
         e2e_s = bc.max_over_ranks((time.perf_counter() - t1) / e2e_steps)
         if Be == B and not all(np.array_equal(r["status"], status) and np.array_equal(u, Ug) for r, u in zip(res, hUs)):
             raise RuntimeError("in-flight host-buffer calls returned results that differ from the device-resident solve")
@@ -378,6 +381,7 @@ def run_nmpc(a, rank, world, local):
                    "batch_total": B_total, "batch_per_gpu": B, "in_flight_batches": L,
                    "in_flight": ("step i runs on lane i mod %d (handle + stream + workspace + host thread each): the latency-bound tail of "
                                  "one batch overlaps the full passes of the next; results bit-identical to single-batch solves" % L) if fl is not None else "one batch at a time",
+                   "lane_stagger_ms": None if fl is None else 1e3 * stagger,
                    "host_wait": None if fl is None else ("sleep on a blocking-sync event" if blocking else "spin"),
                    "N": N, "M": M, "n_obstacles": int(obh.shape[1]), "tol": 1e-8,
                    "solver": {"max_iter": MAX_ITER, "max_soc": 4, "watchdog_trigger": 10, "note": "same on the CPU arm"},

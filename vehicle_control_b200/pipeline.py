@@ -15,6 +15,7 @@ in the same order by every rank).
 from __future__ import annotations
 
 import threading
+import time
 from typing import Callable, List, Optional, Sequence
 
 
@@ -67,16 +68,20 @@ class InFlight:
         return _Ordered(self, i)
 
     def run(self, step_fn: Callable[[Lane, int], None], n_steps: int, first: Optional[Callable[[Lane], None]] = None,
-            last: Optional[Callable[[Lane], None]] = None):
+            last: Optional[Callable[[Lane], None]] = None, stagger_s: float = 0.0):
         """step_fn(lane, i) for i in range(n_steps), step i on lane i mod L, one host thread per lane; `first` / `last`
         run on every lane (in its stream context) before its first / after its last step.  Returns when every lane has
-        issued all its work (not a device synchronisation).  The first exception of a lane is re-raised."""
+        issued all its work (not a device synchronisation).  The first exception of a lane is re-raised.
+        stagger_s: lane l starts l * stagger_s seconds late (lanes that start together reach their tails together; on
+        the C3 bench this made no measurable difference -- the lanes drift apart by themselves)."""
         self._next = 0
         errors: List[BaseException] = []
         L = len(self.lanes)
 
         def loop(lane: Lane):
             try:
+                if stagger_s > 0.0 and lane.index > 0:
+                    time.sleep(lane.index * stagger_s)
                 with lane:
                     if first:
                         first(lane)
