@@ -33,7 +33,7 @@ import bench_common as bc  # noqa: E402
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=8)
+    ap.add_argument("--steps", type=int, default=12)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default=None, choices=["nmpc", "rollout", "c2"])
@@ -45,8 +45,8 @@ def parse():
                     help="strong: the configuration's batch is split over the GPUs; weak: every GPU gets the whole batch")
     ap.add_argument("--in-flight", type=int, default=0, dest="in_flight",
                     help="C3: batches in flight per GPU (lanes: handle + stream + workspace + host thread each); 1 = one batch "
-                         "at a time; 0 = by the per-GPU batch (4 at >= 32,768 instances, 6 at >= 16,384, else 8: the tail of a "
-                         "batch lasts as long whatever its size, so smaller batches need more of them in flight to hide it)")
+                         "at a time; 0 = by the per-GPU batch (6 at >= 16,384 instances, else 8: the tail of a batch lasts as long "
+                         "whatever its size, so smaller batches need more of them in flight to hide it)")
     ap.add_argument("--lap-cache", default=None, help="npz file to save/load the untimed warm-start lap (profiling runs)")
     ap.add_argument("--rollout-batch", type=int, default=0, help="trajectories of the C5 leg (0 = 1,048,576)")
     ap.add_argument("--no-secondary", action="store_true", help="skip the C5 block of the default line")

@@ -226,7 +226,7 @@ def run_nmpc(a, rank, world, local):
     # the latency-bound tail of one batch runs under the full passes of the next; results are bit-identical)
     L = int(getattr(a, "in_flight", 0))
     if L <= 0:
-        L = 4 if B >= 32768 else (6 if B >= 16384 else 8)
+        L = 6 if B >= 16384 else 8
     fl = None
     ms, value, launches_fl = ms_single, value_single, None
     if L > 1:
