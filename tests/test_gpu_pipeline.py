@@ -63,3 +63,24 @@ def test_lanes_return_the_single_handle_results():
     fl.run(hstep, steps)
     for (U, X, st, it), (_, Xh, Uh, _), r in zip(ref, hx, res):
         assert np.array_equal(Uh, U) and np.array_equal(Xh, X) and np.array_equal(r["status"], st) and np.array_equal(r["iters"], it)
+
+
+def test_fleet_in_lanes_equals_single_simulator(golden):
+    """A closed-loop fleet split over lanes (pipeline.run_fleet_in_lanes) ends, vehicle for vehicle and bit for bit, where
+    the single-handle BatchedRacingSimulator ends after the same number of ticks."""
+    from vehicle_control_b200.pipeline import run_fleet_in_lanes
+    from vehicle_control_b200.simulation.racing import BatchedRacingSimulator
+    _, meta = golden
+    cfg = meta["cascaded1_ippodromo/cascaded"]["config"]
+    B, ticks = 24, 25
+    rng = np.random.default_rng(1004)
+    x0 = np.zeros((B, 8)); x0[:, 0] = 4.0; x0[:, 4] = 1.0 + rng.uniform(0, 5, B); x0[:, 5] = rng.uniform(-1, 1, B)
+    car, trk = load_yaml("models/dynamic_car.yaml"), load_yaml("environment/ippodromo.yaml")
+    np.random.seed(31)
+    one = BatchedRacingSimulator(car, trk, cfg, x0, record=False)
+    assert one.run(ticks) == ticks
+    sims = run_fleet_in_lanes(car, trk, cfg, x0, 3, device=torch.cuda.current_device(), max_ticks=ticks)
+    assert [s.B for s in sims] == [8, 8, 8]
+    x = torch.cat([s.x for s in sims]).cpu().numpy()
+    assert np.array_equal(x, one.x.cpu().numpy())
+    assert sum(int(s.total_solves) for s in sims) == int(one.total_solves)

@@ -125,3 +125,35 @@ class _Ordered:
                 self.o._next = self.i + 1
             self.o._cv.notify_all()
         return False
+
+
+def run_fleet_in_lanes(carconfig, trackconfig, controller_config, x0, n_lanes: int, device: int = 0, max_ticks: int = 3000,
+                       obstacles=None, record: bool = False, seed: Optional[int] = 31):
+    """Closed-loop lap of a fleet (BASELINE config C4) with the vehicles split into `n_lanes` contiguous groups, each a
+    BatchedRacingSimulator on a lane of its own.  A closed loop needs every action of a group before its plant step, but
+    the groups do not interact (simulation/racing.py:230-241 of the reference), so while one group's tick is in its
+    latency-bound tail the others' full passes fill the GPU.  Every vehicle's trajectory is what the single-handle
+    simulator gives (instances never influence each other).  `seed`: numpy's legacy generator is seeded with it before
+    each group's controller draws its cold guess (cascaded_mpc.py:13 seeds 31 at import), so every group starts from the
+    guess a single simulator would use.  Returns the list of simulators (group order = vehicle order)."""
+    import numpy as np
+    from .environment.track import Track
+    from .simulation.racing import BatchedRacingSimulator
+    from .utils.common_utils import as_config
+    x0 = np.ascontiguousarray(x0, dtype=float)
+    track = trackconfig if isinstance(trackconfig, Track) else Track(trackconfig)
+    n_lanes = max(1, min(int(n_lanes), len(x0)))
+    fl = InFlight.create(as_config(carconfig), as_config(controller_config), track, device, n_lanes)
+    bounds = [len(x0) * i // n_lanes for i in range(n_lanes + 1)]
+    sims = []
+    for i, lane in enumerate(fl.lanes):          # built one after the other (the cold guess comes from a global generator)
+        ob = None if obstacles is None else obstacles[bounds[i]:bounds[i + 1]]
+        with lane:
+            if seed is not None:
+                np.random.seed(seed)
+            sims.append(BatchedRacingSimulator(carconfig, track, controller_config, x0[bounds[i]:bounds[i + 1]], obstacles=ob,
+                                               record=record, engine=lane.eng))
+        lane.synchronize()
+    fl.run(lambda lane, i: sims[i].run(max_ticks), n_lanes)
+    fl.synchronize()
+    return sims

@@ -177,10 +177,11 @@ class BatchedRacingSimulator:
     """B vehicles, one controller configuration, lock-step ticks, device resident (BASELINE config C4)."""
 
     def __init__(self, carconfig, trackconfig, controller_config, x0, obstacles=None, device=None, record=True,
-                 tracks=None, track_id=None):
+                 tracks=None, track_id=None, engine=None):
         self.track = trackconfig if isinstance(trackconfig, Track) else Track(trackconfig)
         self.config = as_config(controller_config)
-        self.engine = Engine(as_config(carconfig), self.config, self.track, device=device)
+        # engine: an existing handle (e.g. a lane of pipeline.InFlight on its own stream) instead of a new one
+        self.engine = engine if engine is not None else Engine(as_config(carconfig), self.config, self.track, device=device)
         e = self.engine
         x0 = np.ascontiguousarray(x0, dtype=float)
         self.B = x0.shape[0]
