@@ -10,7 +10,7 @@ import time
 import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
-FP64_PEAK_TFLOPS = 37.0   # measured DFMA peak of this pool's B200 (scripts_dev/fp64_peak.cu, profiles/r01_fp64_peak.txt)
+FP64_PEAK_TFLOPS = 37.0   # measured DFMA peak of this pool's B200 (scripts/fp64_peak.cu, profiles/r01_fp64_peak.txt)
 
 
 def load_yaml(rel):
