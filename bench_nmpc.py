@@ -119,13 +119,19 @@ def bytes_per_solve(H):
 
 
 def source_hash():
-    """hash of the CUDA sources the ncu per-unit numbers (profiles/*_ncu_units.json) were captured for"""
+    """hash of the CUDA sources the ncu per-unit numbers (profiles/*_ncu_units.json) were captured for; comments and white
+    space do not count (a comment-only edit leaves the SASS, and therefore the captured numbers, as they are)"""
     import hashlib
+    import re
     h = hashlib.sha256()
     d = os.path.join(bc.ROOT, "vehicle_control_b200", "csrc")
     for f in sorted(os.listdir(d)):
-        with open(os.path.join(d, f), "rb") as fh:
-            h.update(fh.read())
+        with open(os.path.join(d, f), "r", encoding="utf-8", errors="replace") as fh:
+            txt = fh.read()
+        txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
+        txt = re.sub(r"//[^\n]*", "", txt)
+        h.update(f.encode())
+        h.update("".join(txt.split()).encode())
     return h.hexdigest()[:16]
 
 

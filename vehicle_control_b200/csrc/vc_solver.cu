@@ -4,13 +4,17 @@
 // Replaces CascadedMPC.command -> opti.solve() (vehicle_control/controllers/mpc/cascaded_mpc.py:306-314), i.e.
 // CasADi's AD (exact Lagrangian Hessian, "expand": True, :65) + IPOPT (:54-66) + the HSL MA27 LDL^T.
 //
-// Kernels per interior-point iteration (host-driven loop, all instances in lock step, finished ones idle):
-//   k_eval_st / k_eval_pm  one thread per (instance, stage, derivative pair): hyper-dual evaluation of the
-//                          stage Lagrangian -> exact Hessian block, dynamics/constraint Jacobians, gradients.
-//   k_step                 one warp per instance: error / barrier update (warp-shuffle reductions), block
-//                          tridiagonal KKT solve by Riccati recursion staged in shared memory (with the
-//                          delta_w inertia ladder), fraction-to-boundary, filter line search with lanes over
-//                          stages, primal-dual update; restoration substitute = dynamic re-rollout.
+// Kernels per interior-point iteration (host-driven loop, all unfinished instances in lock step; finished ones cost nothing):
+//   k_eval_st              eight threads per (instance, SingleTrack stage): forward in Dual1 arithmetic + the hand-written
+//                          adjoint sweep of vc_adj.cuh -> Jacobian columns, gradient, exact Hessian column (forward over reverse)
+//   k_eval_pm              one thread per (instance, PointMass stage, derivative pair): hyper-dual evaluation
+//   k_step_a               one warp per instance: error / barrier update (warp-shuffle reductions), block tridiagonal KKT
+//                          solve by a Riccati recursion staged in shared memory (delta_w inertia ladder), directions
+//   k_step_b               one warp per instance: fraction to the boundary, filter line search with lanes over stages,
+//                          second-order correction, watchdog (k_step_*_wide: one CTA per instance for the late passes)
+//   k_update               one warp per (instance, stage): the accepted primal-dual step
+// IPOPT's restoration phase is not restated: where it would start, the step is damped, then the iterate is re-initialised
+// by a dynamically feasible rollout, then the instance ends with VC_LINESEARCH_FAIL.
 // All fp64; per-stage matrices are <= 11x11, so there is nothing for tensor cores here.
 #include <cstdio>
 #include <cstring>
