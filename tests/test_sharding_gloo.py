@@ -61,3 +61,42 @@ def test_gather_results_world2_gloo(n):
     for p in ps:
         p.join(60)
     assert res == [(0, True), (1, True)]
+
+
+def _lanes_worker(rank, world, port, n, steps, q):
+    """the strong-scaling bench protocol on the CPU: every rank runs its steps on three lanes (host threads) that finish
+    out of order, and issues the result gather of step i inside InFlight.ordered(i) -- the collectives must pair up"""
+    import random
+    import time
+    from vehicle_control_b200.pipeline import InFlight, Lane
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        fl = InFlight([Lane(i, engine=None, stream=None) for i in range(3)])
+        rnd = random.Random(100 + rank)              # different delays on every rank
+        got = [None] * steps
+
+        def step(lane, i):
+            time.sleep(0.001 * rnd.randint(0, 20))
+            full = torch.arange(n, dtype=torch.float64) * (i + 1)      # step i's "solution"
+            with fl.ordered(i):
+                got[i] = sharding.gather_results({"obj": sharding.shard(full).clone()}, n)["obj"]
+
+        fl.run(step, steps)
+        ok = all(torch.equal(got[i], torch.arange(n, dtype=torch.float64) * (i + 1)) for i in range(steps))
+        q.put((rank, ok))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_in_flight_lanes_gather_in_step_order_world2_gloo():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    ps = [ctx.Process(target=_lanes_worker, args=(r, 2, port, 11, 10, q)) for r in range(2)]
+    for p in ps:
+        p.start()
+    res = sorted(q.get(timeout=180) for _ in ps)
+    for p in ps:
+        p.join(60)
+    assert res == [(0, True), (1, True)]
