@@ -8,8 +8,9 @@ max(0.99, 1-mu), filter line search, inertia correction of the KKT matrix by del
 objective scaling (nlp_scaling_max_gradient 100), bound_relax_factor 1e-8, acceptable_tol 1e-6 / 15
 iterations.  IPOPT is a third-party dependency absent from /root/reference and from this image, so
 this file restates its PUBLISHED algorithm (Waechter & Biegler, Math. Prog. 106, 2006) on a dense
-KKT system with scipy's symmetric-indefinite LDL^T.  It does not implement the restoration phase or
-second-order corrections; those change the path, not the point converged to.
+KKT system with scipy's symmetric-indefinite LDL^T.  It does not implement the restoration phase, the
+second-order correction or the watchdog (oracle/cpp has the last two): they change the iterate path, and
+on a few "branch" ticks of the non-convex NLP also which local solution it ends in.
 
 Parity status: PINNED by the reference's cold-start known answers (tests/test_oracle_nmpc.py).
 """
